@@ -1,0 +1,154 @@
+/* tinyr.h — C ABI of the B200-native rasterization backend for litzendraht/tiny_renderer.
+ *
+ * This is the drop-in boundary.  The reference has no FFI; what it has is the `Scene` public API
+ * (/root/reference/src/scene.rs) driven by app::run (/root/reference/src/app.rs:137-146,170,208-213).
+ * Every entry point below names the reference item it replaces.  Plain pointers and sizes only; no C++,
+ * CUDA or torch types.  All functions return a tr_status (0 = OK, negative = error) unless noted, never
+ * abort the process, and leave a message retrievable with tr_last_error() (thread-local).
+ *
+ * Threading (scene.rs takes &mut self everywhere): a tr_scene is NOT thread-safe; distinct scenes may be
+ * driven from distinct threads.  All device work of a scene is issued on one CUDA stream; tr_scene_render
+ * is asynchronous, every getter synchronises.
+ *
+ * Pixel conventions: the reference's frame_buffer has pixel (0,0) at the bottom-left, index i + j*w
+ * (scene.rs:24,260); Scene::get_frame_buffer returns the vertically flipped (top-down) image
+ * (scene.rs:92-97).  "topdown" getters mirror the reference getters, "raw" getters use i + j*w.
+ */
+#ifndef TINYR_H
+#define TINYR_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TR_VERSION_STRING "tinyr 0.1 (sm_100a)"
+#define TR_NO_TRIANGLE 0xFFFFFFFFu
+
+typedef enum tr_status {
+    TR_OK = 0,
+    TR_ERR_INVALID_ARGUMENT = -1,
+    TR_ERR_UNKNOWN_PIPELINE = -2,     /* reference: panic!("Provided pipeline name is not supported!") shader.rs:108 */
+    TR_ERR_BAD_POLYGON = -3,          /* reference: panic!("Encountered some garbage...") scene.rs:218 */
+    TR_ERR_IO = -4,                   /* reference: `?` on File::open / image::open, app.rs:94,99 */
+    TR_ERR_FORMAT = -5,               /* malformed OBJ / TGA */
+    TR_ERR_CUDA = -6,
+    TR_ERR_NO_DEVICE = -7,            /* no CUDA device: there is NO CPU fallback */
+    TR_ERR_REFERENCE_UNDEFINED = -8,  /* inputs for which the reference panics (singular basis, light = -z in occlusion, ...) */
+    TR_ERR_NCCL = -9,
+    TR_ERR_UNSUPPORTED = -10
+} tr_status;
+
+typedef struct tr_scene tr_scene;
+
+/* image::RgbImage as produced by image::open(..).into_rgb8() (app.rs:99): RGB8, row 0 = top. */
+typedef struct tr_image {
+    const uint8_t* rgb8_topdown;
+    uint32_t width, height;
+} tr_image;
+
+/* Arguments of Scene::new (scene.rs:47-56).  obj::raw::RawObj is flattened to arrays:
+ *   positions  n_positions x 3 (x,y,z; obj `w` is ignored by the reference, util.rs:25-31)
+ *   uvs        n_uvs x 2       (u,v;   3rd component ignored, shader.rs:144)
+ *   normals    n_normals x 3
+ *   tri_idx    n_triangles x 9 (p0 t0 n0 p1 t1 n1 p2 t2 n2), 0-based; only the first three corners of a
+ *              polygon are used by the reference (scene.rs:224-226)
+ * The caller keeps ownership; create copies everything to the device (Model is immutable afterwards). */
+typedef struct tr_scene_desc {
+    uint32_t width, height;
+    const float* positions;   uint32_t n_positions;
+    const float* uvs;         uint32_t n_uvs;
+    const float* normals;     uint32_t n_normals;
+    const uint32_t* tri_idx;  uint32_t n_triangles;
+    tr_image texture, normal_map, normal_map_tangent, specular_map;
+    const char* pipeline_name;   /* default phong normal_map (alias true_normal) specular darboux shadow occlusion */
+    int32_t device;              /* CUDA device ordinal */
+    uint32_t ring;               /* number of frame/visibility buffer sets to rotate through in batch calls (0 -> 1) */
+} tr_scene_desc;
+
+/* ---- Scene surface (scene.rs) ------------------------------------------------------------------------- */
+int tr_scene_create(tr_scene** out, const tr_scene_desc* desc);                  /* Scene::new            scene.rs:47  */
+void tr_scene_destroy(tr_scene* s);                                              /* Drop                                */
+int tr_scene_clear(tr_scene* s);                                                 /* Scene::clear          scene.rs:128 */
+int tr_scene_set_light_direction(tr_scene* s, const float dir[3]);               /* set_light_direction   scene.rs:140 */
+int tr_scene_set_camera(tr_scene* s, const float look_from[3], const float look_at[3], const float up[3]); /* scene.rs:145 */
+int tr_scene_render(tr_scene* s);                                                /* Scene::render         scene.rs:151 */
+int tr_scene_get_frame_buffer(tr_scene* s, uint8_t* dst_rgb8_topdown);           /* get_frame_buffer      scene.rs:92  */
+int tr_scene_get_z_buffer(tr_scene* s, uint8_t* dst_rgb8_topdown);               /* get_z_buffer          scene.rs:101 */
+int tr_scene_get_shadow_buffer(tr_scene* s, uint8_t* dst_rgb8_topdown);          /* get_shadow_buffer     scene.rs:115 */
+
+/* ---- additions: raw state, visibility, diagnostics ---------------------------------------------------- */
+int tr_scene_read_frame_raw(tr_scene* s, uint8_t* dst_rgb8_bottomup);            /* Scene.frame_buffer as stored, i + j*w */
+int tr_scene_read_depth(tr_scene* s, float* dst);                                /* Buffer.z_buffer       shader.rs:18 */
+int tr_scene_read_shadow(tr_scene* s, float* dst);                               /* Buffer.shadow_buffer  shader.rs:19 */
+int tr_scene_read_visibility(tr_scene* s, uint32_t* dst_tri_id);                 /* winning polygon index per pixel, TR_NO_TRIANGLE if none */
+int tr_scene_set_pipeline(tr_scene* s, const char* pipeline_name);               /* ShaderPipeline::new   shader.rs:97 (buffers re-zeroed) */
+int tr_scene_synchronize(tr_scene* s);
+/* out[0] shadow index >= w*h (reference panics, shader.rs:778,912,935)   out[1] round(x) >= w (reference reads the next row)
+ * out[2] texel out of range (reference panics, util.rs:40)                out[3] NaN depth
+ * out[4] homogeneous w == 0 (reference unwrap panic, shader.rs:158)       out[5] singular darboux basis (shader.rs:631)
+ * out[6] triangles binned  out[7] reserved */
+int tr_scene_diagnostics(tr_scene* s, uint64_t out[8]);
+/* The uniforms of the last prepare (shader.rs:183-279), row-major 4x4: vpmv, i_vpmv, m, i_m, it_m, shadow,
+ * then camera_direction[3], t_light_direction[3] — 102 floats. */
+int tr_scene_get_uniforms(tr_scene* s, float out[102]);
+
+/* ---- batch modes (BASELINE.json configs 4 and 5) -------------------------------------------------------- */
+typedef struct tr_view {
+    float look_from[3], look_at[3], up[3], light_direction[3];
+} tr_view;
+/* For each view: set_light_direction, set_camera, clear, render (app.rs:170,208-210).  checksums (optional,
+ * host, n) receives a 64-bit checksum of each top-down RGB8 frame computed on the device (see
+ * tr_checksum_rgb8); frames (optional, host, n*3*w*h) receives every frame. */
+int tr_scene_render_views(tr_scene* s, const tr_view* views, uint32_t n_views, uint64_t* checksums, uint8_t* frames_rgb8_topdown);
+/* Many-light ambient occlusion: for each light `set_light_direction; clear; render` with the occlusion
+ * pipeline (shader.rs:806-963) and accum[i + j*w] += gray (u32).  Camera visibility is computed once.
+ * The sums stay on the device (tr_scene_ao_device_buffer); accum_host (optional) receives a copy.
+ * reset != 0 zeroes the accumulator first. */
+int tr_scene_render_ao(tr_scene* s, const float* light_dirs_xyz, uint32_t n_lights, int reset, uint32_t* accum_host);
+int tr_scene_ao_device_buffer(tr_scene* s, void** device_ptr_u32, size_t* n_elements);
+int tr_scene_read_ao(tr_scene* s, uint32_t* accum_host);
+uint64_t tr_checksum_rgb8(const uint8_t* rgb8, size_t n_bytes);                  /* host twin of the device checksum */
+
+/* ---- device plumbing -------------------------------------------------------------------------------- */
+int tr_device_count(int* n);
+int tr_scene_set_stream(tr_scene* s, void* cuda_stream);                          /* run on the caller's cudaStream_t (NULL = scene's own) */
+int tr_scene_device_frame(tr_scene* s, void** device_ptr_rgb8_topdown);           /* zero-copy access for tests / interop */
+int tr_scene_timer_begin(tr_scene* s);                                            /* CUDA event on the scene stream */
+int tr_scene_timer_end(tr_scene* s, float* elapsed_ms);                           /* records + synchronises */
+/* Per-kernel device times (CUDA events around every launch while enabled).  names: K1 vertex_setup, K2 bin,
+ * K3 raster_visibility, K4 shadow_depth, K5 shade, K6 ao_accumulate, K7 clear/pack, K8 checksum. */
+int tr_scene_set_profiling(tr_scene* s, int enabled);
+int tr_scene_kernel_times(tr_scene* s, float total_ms[8], uint64_t launches[8]);
+void* tr_host_alloc(size_t bytes);                                                /* pinned host memory for fast get_* copies */
+void tr_host_free(void* p);
+
+/* ---- asset loaders kept from the reference (app.rs:87-131) ------------------------------------------- */
+typedef struct tr_mesh {
+    float* positions;   uint32_t n_positions;
+    float* uvs;         uint32_t n_uvs;
+    float* normals;     uint32_t n_normals;
+    uint32_t* tri_idx;  uint32_t n_triangles;
+} tr_mesh;
+typedef struct tr_pixels {
+    uint8_t* rgb8_topdown;
+    uint32_t width, height;
+} tr_pixels;
+int tr_load_obj(const char* path, tr_mesh* out);        /* obj::raw::parse_obj, app.rs:94 (PTN polygons only, scene.rs:216-219) */
+void tr_mesh_free(tr_mesh* m);
+int tr_load_tga(const char* path, tr_pixels* out);      /* image::open(path)?.into_rgb8(), app.rs:99 */
+void tr_pixels_free(tr_pixels* p);
+int tr_write_tga(const char* path, const uint8_t* rgb8_topdown, uint32_t width, uint32_t height, int rle);  /* headless output */
+/* app::run's load sequence (app.rs:87-146): <dir>/model.obj, texture.tga, normal_map.tga, normal_map_tangent.tga, specular_map.tga */
+int tr_scene_create_from_dir(tr_scene** out, const char* asset_dir, const char* pipeline_name, uint32_t width,
+                             uint32_t height, int32_t device, uint32_t ring);
+
+const char* tr_last_error(void);
+const char* tr_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TINYR_H */

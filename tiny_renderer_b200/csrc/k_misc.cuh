@@ -1,0 +1,63 @@
+// k_misc.cuh — K7 clear / views / flips and K8 frame checksum.
+#pragma once
+#include "tr_types.cuh"
+
+namespace tr {
+
+// Scene::clear (/root/reference/src/scene.rs:128-137) materialised, or Buffer::new's zero state
+// (/root/reference/src/scene/shader.rs:46-47) when z_init = 0.  Grid-stride, 16-byte stores where possible.
+__global__ void __launch_bounds__(256) k_fill_state(unsigned long long* keys, float* shadow, uint32_t* rgb_words, size_t n_px,
+                                                    size_t n_rgb_words, float z_init, int do_keys, int do_shadow, int do_rgb) {
+    size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+    const unsigned long long k = make_key(z_init, kNoTri);
+    if (do_keys) for (size_t i = i0; i < n_px; i += stride) keys[i] = k;
+    if (do_shadow) for (size_t i = i0; i < n_px; i += stride) shadow[i] = z_init;
+    if (do_rgb) for (size_t i = i0; i < n_rgb_words; i += stride) rgb_words[i] = 0u;
+}
+
+// Raw bottom-up views of the state the reference keeps in Buffer.z_buffer / visibility (derived from keys).
+__global__ void __launch_bounds__(256) k_unpack_keys(const unsigned long long* keys, float* depth, uint32_t* tri, size_t n_px) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_px) return;
+    unsigned long long k = keys[i];
+    if (depth) depth[i] = key_depth(k);
+    if (tri) tri[i] = key_lo(k) == kNoTri ? kNoTri : (key_lo(k) & kTriMask);
+}
+
+// get_z_buffer / get_shadow_buffer (scene.rs:101-125): saturating `f32 as u8` gray, vertically flipped.
+__global__ void __launch_bounds__(256) k_gray_view(const unsigned long long* keys, const float* plane, uint8_t* dst, uint32_t w, uint32_t h) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)w * h) return;
+    uint32_t x = (uint32_t)(i % w), y = (uint32_t)(i / w);
+    float v = keys ? key_depth(keys[i]) : plane[i];
+    uint8_t g = (uint8_t)cast_u8(v);
+    uint8_t* p = dst + ((size_t)(h - 1 - y) * w + x) * 3;
+    p[0] = g; p[1] = g; p[2] = g;
+}
+
+// Vertical flip of an RGB8 image (top-down storage -> the reference's bottom-up frame_buffer order).
+__global__ void __launch_bounds__(256) k_flip_rows(const uint8_t* src, uint8_t* dst, uint32_t row_bytes, uint32_t h) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)row_bytes * h) return;
+    uint32_t y = (uint32_t)(i / row_bytes), b = (uint32_t)(i % row_bytes);
+    dst[(size_t)(h - 1 - y) * row_bytes + b] = src[i];
+}
+
+// K8: position-weighted 64-bit checksum of a byte image viewed as little-endian u32 words:
+// sum_i word_i * (2 i + 1) mod 2^64 (tr_checksum_rgb8 is the host twin).  n_words = bytes / 4 (bytes % 4 == 0).
+__global__ void __launch_bounds__(256) k_checksum(const uint32_t* words, size_t n_words, unsigned long long* out) {
+    size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+    unsigned long long acc = 0;
+    for (size_t i = i0; i < n_words; i += stride) acc += (unsigned long long)__ldg(&words[i]) * (2ull * i + 1ull);
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    __shared__ unsigned long long s[8];
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+        for (int w = 0; w < 8; ++w) t += s[w];
+        atomicAdd(out, t);
+    }
+}
+
+}  // namespace tr

@@ -1,0 +1,109 @@
+// k_setup.cuh — K1 vertex_setup: one thread per polygon, coalesced float4 loads of the corner-expanded
+// static geometry, SoA setup records out.  Replaces the reference's vertex closures
+// (/root/reference/src/scene/shader.rs:285-316, 349-384, 416-437, 475-496, 549-595, 671-692, 711-747,
+// 809-830, 849-870), their helpers (shader.rs:116-165) and the bounding box of scene.rs:232-239.
+#pragma once
+#include "tr_types.cuh"
+
+namespace tr {
+
+// Static per-polygon geometry, written once at scene creation (24 floats = 6 x float4):
+//   [0..8]  p0 p1 p2 (xyz)   [9..14] u0 u1 u2 v0' v1' v2' with v' = 1 - v   [15..23] n0 n1 n2 (xyz)
+constexpr int kStaticWords = 24;
+
+struct SetupOut {
+    float4* rec;      // n_triangles x 4 float4 (kRecWords)
+    float4* var;      // n_triangles x 6 float4 (kVarWords), may be null when the pipeline needs none
+    int4* bbox;       // n_triangles: xmin ymin xmax ymax clamped to the screen; xmin > xmax when not drawn
+};
+
+// it_m * (n, 0) -> must have w == 0 -> normalised   (shader.rs:300-303, 368-371)
+__device__ __forceinline__ f3 normal_to_camera(const Uniforms& u, f3 n, unsigned long long* diag) {
+    f4 t = xform(u.it_m, f4{n.x, n.y, n.z, 0.0f});
+    if (!(t.w == 0.0f)) atomicAdd(&diag[D_W_ZERO], 1ull);
+    return unit3(f3{t.x, t.y, t.z});
+}
+
+// LIGHT_PASS: shadow/occlusion pass 1 — no culling, transform by u.shadow, no varyings.
+template <bool LIGHT_PASS>
+__global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__ geom, SetupOut out, const Uniforms u,
+                                                     int pipeline, unsigned long long* diag) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= u.n_triangles) return;
+    float g[kStaticWords];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        float4 v = __ldg(&geom[(size_t)t * 6 + k]);
+        g[4 * k] = v.x; g[4 * k + 1] = v.y; g[4 * k + 2] = v.z; g[4 * k + 3] = v.w;
+    }
+    f3 p[3] = {{g[0], g[1], g[2]}, {g[3], g[4], g[5]}, {g[6], g[7], g[8]}};
+    bool drawn = true;
+    f3 face_normal{0.0f, 0.0f, 0.0f};
+    if (!LIGHT_PASS) {
+        // should_cull_face, shader.rs:116-124 (object-space normal against camera_direction)
+        face_normal = cross3(p[1] - p[0], p[2] - p[0]);
+        drawn = !(dot3(u.camera_direction, face_normal) <= 0.0f);
+    }
+    // store_vertex_transformation_results, shader.rs:150-165
+    const mat4& M = LIGHT_PASS ? u.shadow : u.vpmv;
+    int32_t rx[3], ry[3];
+    float rz[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        bool ok;
+        f3 s = dehomog(xform(M, f4{p[i].x, p[i].y, p[i].z, 1.0f}), ok);
+        if (!ok && drawn) atomicAdd(&diag[D_W_ZERO], 1ull);
+        rx[i] = cast_i32(s.x);
+        ry[i] = cast_i32(s.y);
+        rz[i] = s.z;
+    }
+    // scene.rs:232-239
+    int32_t xmin = max(0, min(min(rx[0], rx[1]), rx[2])), xmax = min(max(max(rx[0], rx[1]), rx[2]), (int32_t)u.width - 1);
+    int32_t ymin = max(0, min(min(ry[0], ry[1]), ry[2])), ymax = min(max(max(ry[0], ry[1]), ry[2]), (int32_t)u.height - 1);
+    if (!drawn || ymin > ymax) { xmin = 1; xmax = 0; }
+    out.bbox[t] = make_int4(xmin, ymin, xmax, ymax);
+
+    float4* rec = out.rec + (size_t)t * 4;
+    rec[0] = make_float4(__int_as_float(rx[0]), __int_as_float(ry[0]), __int_as_float(rx[1]), __int_as_float(ry[1]));
+    rec[1] = make_float4(__int_as_float(rx[2]), __int_as_float(ry[2]), rz[0], rz[1]);
+    rec[2] = make_float4(rz[2], __int_as_float(drawn ? kFlagDrawn : 0u), g[9], g[10]);
+    rec[3] = make_float4(g[11], g[12], g[13], g[14]);
+    if (LIGHT_PASS || !drawn || out.var == nullptr) return;
+
+    float v[kVarWords];
+#pragma unroll
+    for (int k = 0; k < kVarWords; ++k) v[k] = 0.0f;
+    f3 nrm[3] = {{g[15], g[16], g[17]}, {g[18], g[19], g[20]}, {g[21], g[22], g[23]}};
+    if (pipeline == P_DEFAULT) {
+        // shader.rs:297-305
+        float d = dot3(u.t_light, normal_to_camera(u, face_normal, diag));
+        v[0] = d; v[1] = d; v[2] = d;
+    } else if (pipeline == P_PHONG || pipeline == P_SHADOW) {
+        // shader.rs:362-373, 725-736
+#pragma unroll
+        for (int i = 0; i < 3; ++i) v[i] = dot3(u.t_light, normal_to_camera(u, nrm[i], diag));
+    } else if (pipeline == P_DARBOUX) {
+        // shader.rs:562-584; rows 0 and 1 of the fragment shader's local basis (shader.rs:612-623) are
+        // constant per polygon: unit(P*(-1,1,0)), unit(P*(-1,0,1)) with P = columns m*p_i.
+        f3 tp[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            bool ok;
+            tp[i] = dehomog(xform(u.m, f4{p[i].x, p[i].y, p[i].z, 1.0f}), ok);
+        }
+        mat3 P = {{tp[0].x, tp[1].x, tp[2].x, tp[0].y, tp[1].y, tp[2].y, tp[0].z, tp[1].z, tp[2].z}};
+        f3 r0 = unit3(xform(P, f3{-1.0f, 1.0f, 0.0f}));
+        f3 r1 = unit3(xform(P, f3{-1.0f, 0.0f, 1.0f}));
+        v[3] = r0.x; v[4] = r0.y; v[5] = r0.z; v[6] = r1.x; v[7] = r1.y; v[8] = r1.z;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            f3 n = normal_to_camera(u, nrm[i], diag);
+            v[12 + 3 * i] = n.x; v[13 + 3 * i] = n.y; v[14 + 3 * i] = n.z;   // column i of vertex_t_normals
+        }
+    }
+    float4* var = out.var + (size_t)t * 6;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) var[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+}
+
+}  // namespace tr

@@ -1,0 +1,191 @@
+// k_shade.cuh — K5 deferred shading (seven pipelines) and K6 ambient-occlusion accumulation.
+//
+// One thread shades four horizontally adjacent pixels: it reads their visibility keys, re-derives the
+// barycentric coordinates of the winning polygon with the reference's arithmetic, runs the pipeline's
+// fragment math and writes 12 contiguous bytes of top-down RGB8.  Texels are point-sampled through texture
+// objects (the texture path).  Replaces the fragment closures of /root/reference/src/scene/shader.rs
+// (:318-333 default, :386-401 phong, :439-459 normal_map, :498-534 specular, :597-655 darboux, :749-788 shadow,
+// :872-947 occlusion), the samplers of /root/reference/src/scene/util.rs:34-83 and color_blend (util.rs:7-13).
+#pragma once
+#include <cuda_runtime.h>
+#include "k_raster.cuh"
+
+namespace tr {
+
+struct Maps {
+    cudaTextureObject_t tex[4];     // texture, normal_map, normal_map_tangent, specular_map (RGBA8, point, unnormalised)
+    uint32_t w[4], h[4];
+};
+
+struct ShadeArgs {
+    const unsigned long long* keys;
+    const float4* rec;
+    const float4* var;
+    const float* shadow;
+    uint8_t* rgb;                   // top-down: row (height-1-j)
+    uint32_t* ao_accum;             // K6: bottom-up u32 sums (index i + j*w)
+    unsigned long long* diag;
+    Maps maps;
+    int fresh;                      // frame was cleared: pixels not shaded now are written as (0,0,0)
+};
+
+// util.rs:34-41 addressing: (uv * size) as u32, image::get_pixel panics when outside -> counted, clamped.
+__device__ __forceinline__ uchar4 fetch_texel(const Maps& mp, int which, int size_of, f2 uv, unsigned long long* diag) {
+    uint32_t x = cast_u32(uv.x * (float)mp.w[size_of]), y = cast_u32(uv.y * (float)mp.h[size_of]);
+    if (x >= mp.w[which] || y >= mp.h[which]) {
+        atomicAdd(&diag[D_TEXEL_OOB], 1ull);
+        x = min(x, mp.w[which] - 1); y = min(y, mp.h[which] - 1);
+    }
+    return tex2D<uchar4>(mp.tex[which], (float)x + 0.5f, (float)y + 0.5f);
+}
+// util.rs:51-56 / 67-72
+__device__ __forceinline__ f3 decode_normal(uchar4 c) {
+    return unit3(f3{(float)c.x / 255.0f - 0.5f, (float)c.y / 255.0f - 0.5f, (float)c.z / 255.0f - 0.5f});
+}
+// color_blend(c, (0,0,0), t), util.rs:7-13
+__device__ __forceinline__ uint32_t blend_black(uint32_t c, float t) { return cast_u8(t * (float)c + (1.0f - t) * 0.0f); }
+__device__ __forceinline__ uint32_t pack_rgb(uint32_t r, uint32_t g, uint32_t b) { return r | (g << 8) | (b << 16); }
+
+// Shadow-buffer lookup of shader.rs:774-778 / 909-912 / 932-935: round, saturating cast, wrapping u32 index.
+__device__ __forceinline__ float shadow_lookup(const float* shadow, f3 s, uint32_t width, uint32_t n_px, unsigned long long* diag) {
+    uint32_t sx = cast_u32(roundf(s.x)), sy = cast_u32(roundf(s.y));
+    if (sx >= width) atomicAdd(&diag[D_SHADOW_XWRAP], 1ull);
+    uint32_t idx = sx + sy * width;
+    if (idx >= n_px) { atomicAdd(&diag[D_SHADOW_OOB], 1ull); return -3.402823466e38f; }
+    return __ldg(&shadow[idx]);
+}
+
+// Fragment math of one pipeline for one covered pixel; returns packed RGB.
+template <int PIPE>
+__device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Uniforms& u, uint32_t tri, int px, int py) {
+    const float4* r = a.rec + (size_t)tri * 4;
+    float4 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2), r3 = __ldg(r + 3);
+    float z, b0, b1, b2;
+    fragment_depth(__float_as_int(r0.x), __float_as_int(r0.y), __float_as_int(r0.z), __float_as_int(r0.w),
+                   __float_as_int(r1.x), __float_as_int(r1.y), r1.z, r1.w, r2.x, px, py, z, b0, b1, b2);
+    // uv = vertex_uvs * bar (2x3 mat-vec, column order)
+    f2 uv{(r2.z * b0 + r2.w * b1) + r3.x * b2, (r3.y * b0 + r3.z * b1) + r3.w * b2};
+    const float4* v = a.var + (size_t)tri * 6;
+
+    if (PIPE == P_OCCLUSION) {
+        // shader.rs:882-947 with the per-pass constants hoisted into Uniforms by K0
+        const uint32_t n_px = u.width * u.height;
+        f4 frag{(float)px, (float)py, z, 1.0f};
+        bool ok1, ok2;
+        f3 wp = dehomog(xform(u.i_vpmv, frag), ok1);
+        f3 fs = dehomog(xform(u.shadow_from_screen, frag), ok2);
+        if (!ok1 || !ok2) atomicAdd(&a.diag[D_W_ZERO], 1ull);
+        float fsv = shadow_lookup(a.shadow, fs, u.width, n_px, a.diag);
+        float occ = 1.0f;
+#pragma unroll 4
+        for (int k = 0; k < 16; ++k) {
+            f3 sp = wp + u.ao_step[k];
+            bool ok;
+            f3 sc = dehomog(xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f}), ok);
+            if (!ok) atomicAdd(&a.diag[D_W_ZERO], 1ull);
+            float sv = shadow_lookup(a.shadow, sc, u.width, n_px, a.diag);
+            if (sv - 1.0f > fsv) {
+                float strength = fminf((sv - fsv) / 20.0f, 1.0f);
+                occ -= 0.0625f * strength;
+            }
+        }
+        uint32_t g = cast_u8(occ * 255.0f + (1.0f - occ) * 0.0f);
+        return pack_rgb(g, g, g);
+    }
+
+    uchar4 c = fetch_texel(a.maps, 0, 0, uv, a.diag);
+    float diff;
+    if (PIPE == P_DEFAULT) {
+        diff = __ldg(&v[0]).x;                                                   // shader.rs:329
+    } else if (PIPE == P_PHONG || PIPE == P_SHADOW) {
+        float4 in = __ldg(&v[0]);
+        diff = (b0 * in.x + b1 * in.y) + b2 * in.z;                              // shader.rs:397, 784
+        if (PIPE == P_SHADOW) {
+            bool ok;
+            f3 s = dehomog(xform(u.shadow_from_screen, f4{(float)px, (float)py, z, 1.0f}), ok);
+            if (!ok) atomicAdd(&a.diag[D_W_ZERO], 1ull);
+            float sv = shadow_lookup(a.shadow, s, u.width, u.width * u.height, a.diag);
+            float coef = (s.z + 1.0f < sv) ? 0.3f : 1.0f;                         // shader.rs:776-780
+            diff = diff * coef;
+        }
+    } else if (PIPE == P_NORMAL_MAP || PIPE == P_SPECULAR) {
+        f3 nm = decode_normal(fetch_texel(a.maps, 1, 1, uv, a.diag));
+        f4 t = xform(u.it_m, f4{nm.x, nm.y, nm.z, 0.0f});
+        f3 n = unit3(f3{t.x, t.y, t.z});                                          // shader.rs:451-454
+        diff = dot3(u.t_light, n);
+        if (PIPE == P_SPECULAR) {
+            f3 refl = unit3((n * dot3(u.t_light, n)) * 2.0f - u.t_light);         // shader.rs:515-518
+            float e = (float)fetch_texel(a.maps, 3, 3, uv, a.diag).x;              // util.rs:82: raw 0..255
+            float spec = 0.6f * powf(fmaxf(refl.z, 0.0f), e);
+            float k = diff + spec;
+            return pack_rgb(cast_u8(fminf(k * (float)c.x, 255.0f)), cast_u8(fminf(k * (float)c.y, 255.0f)),
+                            cast_u8(fminf(k * (float)c.z, 255.0f)));               // shader.rs:526-530
+        }
+    } else {   // P_DARBOUX, shader.rs:608-651
+        f3 nt = decode_normal(fetch_texel(a.maps, 2, 1, uv, a.diag));             // util.rs:61-63: sized by normal_map
+        float4 v0 = __ldg(&v[0]), v1 = __ldg(&v[1]), v2 = __ldg(&v[2]), v3 = __ldg(&v[3]), v4 = __ldg(&v[4]), v5 = __ldg(&v[5]);
+        mat3 N = {{v3.x, v3.w, v4.z, v3.y, v4.x, v4.w, v3.z, v4.y, v5.x}};         // vertex_t_normals, columns n0 n1 n2
+        f3 local_z = xform(N, f3{b0, b1, b2});
+        f3 row2 = unit3(local_z);
+        // A rows: (v0.w v1.x v1.y), (v1.z v1.w v2.x), row2 — inverse by minors, each entry divided by det
+        float m11 = v0.w, m12 = v1.x, m13 = v1.y, m21 = v1.z, m22 = v1.w, m23 = v2.x, m31 = row2.x, m32 = row2.y, m33 = row2.z;
+        float mi1 = m22 * m33 - m32 * m23, mi2 = m21 * m33 - m31 * m23, mi3 = m21 * m32 - m31 * m22;
+        float det = m11 * mi1 - m12 * mi2 + m13 * mi3;
+        if (det == 0.0f) { atomicAdd(&a.diag[D_SINGULAR_BASIS], 1ull); return 0u; }
+        mat3 I = {{mi1 / det, (m13 * m32 - m33 * m12) / det, (m12 * m23 - m22 * m13) / det,
+                   -mi2 / det, (m11 * m33 - m31 * m13) / det, (m13 * m21 - m23 * m11) / det,
+                   mi3 / det, (m12 * m31 - m32 * m11) / det, (m11 * m22 - m21 * m12) / det}};
+        // uvs: r2.z r2.w r3.x = u0 u1 u2 ; r3.y r3.z r3.w = v0 v1 v2
+        f3 lx = unit3(xform(I, f3{r2.w - r2.z, r3.x - r2.z, 0.0f}));
+        f3 ly = unit3(xform(I, f3{r3.z - r3.y, r3.w - r3.y, 0.0f}));
+        f3 lz = unit3(local_z);
+        mat3 B = {{lx.x, ly.x, lz.x, lx.y, ly.y, lz.y, lx.z, ly.z, lz.z}};
+        f3 n = unit3(xform(B, nt));
+        diff = dot3(u.t_light, n);
+    }
+    return pack_rgb(blend_black(c.x, diff), blend_black(c.y, diff), blend_black(c.z, diff));
+}
+
+// ACCUM: K6 — add the occlusion gray of every covered pixel into ao_accum instead of writing RGB.
+template <int PIPE, bool ACCUM>
+__global__ void __launch_bounds__(256) k_shade(const ShadeArgs a, const Uniforms u) {
+    const uint32_t groups_per_row = (u.width + 3) / 4;
+    uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= groups_per_row * u.height) return;
+    const int py = (int)(gid / groups_per_row), px0 = (int)(gid % groups_per_row) * 4;
+    uint32_t out[4];
+    bool shaded[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        int px = px0 + k;
+        out[k] = 0u; shaded[k] = false;
+        if (px >= (int)u.width) continue;
+        unsigned long long key = __ldg(&a.keys[(size_t)py * u.width + px]);
+        uint32_t lo = key_lo(key);
+        // Only fragments that passed the depth test in THIS render are shaded (earlier renders keep their colour).
+        if (lo == kNoTri || (lo >> 24) != (ACCUM ? 0u : u.epoch)) continue;
+        out[k] = shade_pixel<PIPE>(a, u, lo & kTriMask, px, py);
+        shaded[k] = true;
+    }
+    if (ACCUM) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (shaded[k]) a.ao_accum[(size_t)py * u.width + px0 + k] += out[k] & 0xffu;
+        return;
+    }
+    uint8_t* row = a.rgb + (size_t)(u.height - 1 - py) * u.width * 3;
+    if (a.fresh && (u.width & 3u) == 0u) {
+        uint32_t w0 = out[0] | (out[1] << 24), w1 = (out[1] >> 8) | (out[2] << 16), w2 = (out[2] >> 16) | (out[3] << 8);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(row + (size_t)px0 * 3);
+        dst[0] = w0; dst[1] = w1; dst[2] = w2;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            int px = px0 + k;
+            if (px >= (int)u.width || !(shaded[k] || a.fresh)) continue;
+            row[px * 3 + 0] = (uint8_t)(out[k]); row[px * 3 + 1] = (uint8_t)(out[k] >> 8); row[px * 3 + 2] = (uint8_t)(out[k] >> 16);
+        }
+    }
+}
+
+}  // namespace tr
