@@ -115,7 +115,6 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a) {
         }
         const int n_list = s_count;
         scan_from = (uint32_t)s_next;   // == n_triangles when everything was staged
-        if (tid == 0 && !DEPTH_ONLY && blockIdx.x == 0 && blockIdx.y == 0) { /* keep diag slot warm */ }
 
         // ---- (2) per-warp blocks: ballot the staged bboxes against the block, evaluate per pixel ----
 #pragma unroll

@@ -1,0 +1,508 @@
+// tinyr.cu — host driver behind the C ABI of include/tinyr.h: owns the device state of a scene and issues
+// K0 (host prepare) -> K1 vertex_setup -> K3 raster_visibility [K4 shadow_depth first for two-pass pipelines]
+// -> K5 shade on one CUDA stream.  Mirrors the reference's Scene (/root/reference/src/scene.rs:25-151).
+// There is no CPU fallback: every entry point fails with TR_ERR_NO_DEVICE / TR_ERR_CUDA without a GPU.
+#include "../../include/tinyr.h"
+#include "tr_error.h"
+#include "tr_prepare.h"
+#include "k_setup.cuh"
+#include "k_raster.cuh"
+#include "k_shade.cuh"
+#include "k_misc.cuh"
+
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace tr;
+
+#define CU(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) return fail(TR_ERR_CUDA, "%s -> %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+enum KernelSlot { KS_SETUP = 0, KS_BIN, KS_RASTER, KS_SHADOW, KS_SHADE, KS_AO, KS_CLEAR, KS_CHECKSUM, KS_COUNT };
+
+struct tr_scene {
+    int device = 0;
+    uint32_t width = 0, height = 0, n_tri = 0, ring = 1, cur = 0;
+    size_t n_px = 0;
+    int pipeline = P_DEFAULT;
+    // reference Scene state (scene.rs:32-35, defaults :66-69)
+    f3 light{0.0f, 0.0f, -1.0f}, from{0.0f, 0.0f, 1.0f}, at{0.0f, 0.0f, 0.0f}, up{0.0f, 1.0f, 0.0f};
+    Uniforms uni{};            // last camera-pass uniforms (for tr_scene_get_uniforms)
+    uint32_t epoch = 0;        // renders since the last clear
+    bool fresh_keys = false, fresh_rgb = false, fresh_shadow = false;   // a clear is pending (folded into the next render)
+    // device
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    float4* geom = nullptr;
+    SetupOut cam{}, lit{};
+    std::vector<unsigned long long*> keys;
+    std::vector<uint8_t*> rgb;
+    float* shadow = nullptr;
+    uint32_t* ao = nullptr;
+    unsigned long long* diag = nullptr;
+    unsigned long long* d_checksums = nullptr; size_t checksum_cap = 0;
+    uint8_t* scratch = nullptr; size_t scratch_bytes = 0;
+    cudaArray_t arrays[4] = {nullptr, nullptr, nullptr, nullptr};
+    Maps maps{};
+    // timing
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    bool profiling = false;
+    struct Span { int slot; cudaEvent_t a, b; };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> event_pool;
+    float kernel_ms[KS_COUNT] = {0};
+    uint64_t kernel_launches[KS_COUNT] = {0};
+};
+
+namespace {
+
+int pipeline_from_name(const char* name) {
+    if (!name) return -1;
+    static const struct { const char* n; int p; } table[] = {
+        {"default", P_DEFAULT}, {"phong", P_PHONG}, {"normal_map", P_NORMAL_MAP}, {"true_normal", P_NORMAL_MAP},
+        {"specular", P_SPECULAR}, {"darboux", P_DARBOUX}, {"shadow", P_SHADOW}, {"occlusion", P_OCCLUSION}};
+    for (auto& e : table) if (strcmp(e.n, name) == 0) return e.p;
+    return -1;
+}
+
+bool two_pass(int p) { return p == P_SHADOW || p == P_OCCLUSION; }
+
+int ensure_scratch(tr_scene* s, size_t bytes) {
+    if (s->scratch_bytes >= bytes) return TR_OK;
+    if (s->scratch) cudaFree(s->scratch);
+    s->scratch = nullptr; s->scratch_bytes = 0;
+    CU(cudaMalloc(&s->scratch, bytes));
+    s->scratch_bytes = bytes;
+    return TR_OK;
+}
+
+// Profiling spans: CUDA events around a launch while tr_scene_set_profiling is on.
+struct Scoped {
+    tr_scene* s; int slot; cudaEvent_t a = nullptr, b = nullptr;
+    cudaEvent_t grab() {
+        cudaEvent_t e;
+        if (!s->event_pool.empty()) { e = s->event_pool.back(); s->event_pool.pop_back(); }
+        else cudaEventCreate(&e);
+        return e;
+    }
+    Scoped(tr_scene* s_, int slot_) : s(s_), slot(slot_) {
+        s->kernel_launches[slot]++;
+        if (s->profiling) { a = grab(); b = grab(); cudaEventRecord(a, s->stream); }
+    }
+    ~Scoped() {
+        if (s->profiling) { cudaEventRecord(b, s->stream); s->spans.push_back({slot, a, b}); }
+    }
+};
+
+int launch_ok(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(TR_ERR_CUDA, "launch of %s failed: %s", what, cudaGetErrorString(e));
+    return TR_OK;
+}
+
+int fill_state(tr_scene* s, float z_init, bool do_keys, bool do_shadow, bool do_rgb) {
+    if (!do_keys && !do_shadow && !do_rgb) return TR_OK;
+    Scoped sp(s, KS_CLEAR);
+    k_fill_state<<<148 * 8, 256, 0, s->stream>>>(s->keys[s->cur], s->shadow, reinterpret_cast<uint32_t*>(s->rgb[s->cur]), s->n_px,
+                                                 (s->n_px * 3 + 3) / 4, z_init, do_keys, do_shadow, do_rgb);
+    return launch_ok("k_fill_state");
+}
+
+// Turn pending (lazy) clears into memory contents, for getters that read state a render has not rewritten.
+int materialise(tr_scene* s) {
+    int rc = fill_state(s, -3.402823466e38f, s->fresh_keys, s->fresh_shadow, s->fresh_rgb);
+    s->fresh_keys = s->fresh_shadow = s->fresh_rgb = false;
+    return rc;
+}
+
+int prep_error(int rc) {
+    switch (rc) {
+        case PREP_SINGULAR: return fail(TR_ERR_REFERENCE_UNDEFINED, "singular transform: the reference panics on try_inverse().unwrap() (shader.rs:224,277,278)");
+        case PREP_LIGHT_W: return fail(TR_ERR_REFERENCE_UNDEFINED, "Vector3::from_homogeneous on w != 0: the reference panics (shader.rs:227,885)");
+        case PREP_ROTATION: return fail(TR_ERR_REFERENCE_UNDEFINED, "light direction antiparallel to +z: Rotation3::rotation_between is None and the reference panics (shader.rs:921)");
+        default: return TR_OK;
+    }
+}
+
+int upload_map(tr_scene* s, int k, const tr_image& img) {
+    if (!img.rgb8_topdown || img.width == 0 || img.height == 0) return fail(TR_ERR_INVALID_ARGUMENT, "map %d is empty", k);
+    std::vector<uchar4> rgba((size_t)img.width * img.height);
+    for (size_t i = 0; i < rgba.size(); ++i)
+        rgba[i] = make_uchar4(img.rgb8_topdown[3 * i], img.rgb8_topdown[3 * i + 1], img.rgb8_topdown[3 * i + 2], 255);
+    cudaChannelFormatDesc fmt = cudaCreateChannelDesc<uchar4>();
+    CU(cudaMallocArray(&s->arrays[k], &fmt, img.width, img.height));
+    CU(cudaMemcpy2DToArray(s->arrays[k], 0, 0, rgba.data(), (size_t)img.width * 4, (size_t)img.width * 4, img.height, cudaMemcpyHostToDevice));
+    cudaResourceDesc res{};
+    res.resType = cudaResourceTypeArray;
+    res.res.array.array = s->arrays[k];
+    cudaTextureDesc td{};
+    td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+    td.filterMode = cudaFilterModePoint;       // nearest texel, like util.rs:34-41
+    td.readMode = cudaReadModeElementType;
+    td.normalizedCoords = 0;
+    CU(cudaCreateTextureObject(&s->maps.tex[k], &res, &td, nullptr));
+    s->maps.w[k] = img.width; s->maps.h[k] = img.height;
+    return TR_OK;
+}
+
+int alloc_setup(SetupOut* o, uint32_t n_tri, bool with_var) {
+    size_t n = n_tri ? n_tri : 1;
+    CU(cudaMalloc(&o->rec, n * kRecWords * 4));
+    CU(cudaMalloc(&o->bbox, n * sizeof(int4)));
+    o->var = nullptr;
+    if (with_var) CU(cudaMalloc(&o->var, n * kVarWords * 4));
+    return TR_OK;
+}
+
+// Buffer::new (shader.rs:41-50): z and shadow buffers start at 0.0 (NOT f32::MIN), frame at 0.
+int reset_to_new(tr_scene* s) {
+    for (uint32_t r = 0; r < s->ring; ++r) {
+        s->cur = r;
+        int rc = fill_state(s, 0.0f, true, r == 0, true);
+        if (rc) return rc;
+    }
+    s->cur = 0;
+    s->epoch = 0;
+    s->fresh_keys = s->fresh_rgb = s->fresh_shadow = false;
+    return TR_OK;
+}
+
+int create_impl(tr_scene* s, const tr_scene_desc* d) {
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) { cudaGetLastError(); return fail(TR_ERR_NO_DEVICE, "no CUDA device (this backend has no CPU fallback)"); }
+    if (d->device < 0 || d->device >= n_dev) return fail(TR_ERR_INVALID_ARGUMENT, "device %d out of range (have %d)", d->device, n_dev);
+    s->device = d->device;
+    CU(cudaSetDevice(s->device));
+    s->pipeline = pipeline_from_name(d->pipeline_name);
+    if (s->pipeline < 0) return fail(TR_ERR_UNKNOWN_PIPELINE, "Provided pipeline name is not supported! (%s)", d->pipeline_name ? d->pipeline_name : "null");
+    if (d->width == 0 || d->height == 0 || d->width > 32768 || d->height > 32768) return fail(TR_ERR_INVALID_ARGUMENT, "bad frame size %ux%u", d->width, d->height);
+    if (d->n_triangles > kMaxTriangles) return fail(TR_ERR_UNSUPPORTED, "more than %u polygons", kMaxTriangles);
+    if ((d->n_triangles && (!d->tri_idx || !d->positions || !d->uvs || !d->normals))) return fail(TR_ERR_INVALID_ARGUMENT, "null geometry array");
+    s->width = d->width; s->height = d->height; s->n_tri = d->n_triangles;
+    s->n_px = (size_t)d->width * d->height;
+    s->ring = d->ring ? d->ring : 1;
+
+    // Corner-expanded static geometry: 24 floats per polygon (k_setup.cuh), v flipped here (shader.rs:144).
+    std::vector<float> g((size_t)(s->n_tri ? s->n_tri : 1) * kStaticWords, 0.0f);
+    for (uint32_t t = 0; t < s->n_tri; ++t) {
+        const uint32_t* ix = d->tri_idx + (size_t)9 * t;
+        float* o = &g[(size_t)t * kStaticWords];
+        for (int c = 0; c < 3; ++c) {
+            uint32_t p = ix[3 * c], tx = ix[3 * c + 1], n = ix[3 * c + 2];
+            if (p >= d->n_positions || tx >= d->n_uvs || n >= d->n_normals) return fail(TR_ERR_BAD_POLYGON, "polygon %u: index out of range", t);
+            o[3 * c] = d->positions[3 * p]; o[3 * c + 1] = d->positions[3 * p + 1]; o[3 * c + 2] = d->positions[3 * p + 2];
+            o[9 + c] = d->uvs[2 * tx];
+            o[12 + c] = 1.0f - d->uvs[2 * tx + 1];
+            o[15 + 3 * c] = d->normals[3 * n]; o[16 + 3 * c] = d->normals[3 * n + 1]; o[17 + 3 * c] = d->normals[3 * n + 2];
+        }
+    }
+    CU(cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking));
+    s->stream = s->own_stream;
+    CU(cudaMalloc(&s->geom, g.size() * 4));
+    CU(cudaMemcpy(s->geom, g.data(), g.size() * 4, cudaMemcpyHostToDevice));
+    int rc;
+    if ((rc = alloc_setup(&s->cam, s->n_tri, true))) return rc;
+    if ((rc = alloc_setup(&s->lit, s->n_tri, false))) return rc;
+    s->keys.assign(s->ring, nullptr); s->rgb.assign(s->ring, nullptr);
+    for (uint32_t r = 0; r < s->ring; ++r) {
+        CU(cudaMalloc(&s->keys[r], s->n_px * 8));
+        CU(cudaMalloc(&s->rgb[r], s->n_px * 3 + 16));
+    }
+    CU(cudaMalloc(&s->shadow, s->n_px * 4));
+    CU(cudaMalloc(&s->ao, s->n_px * 4));
+    CU(cudaMemset(s->ao, 0, s->n_px * 4));
+    CU(cudaMalloc(&s->diag, D_COUNT * 8));
+    CU(cudaMemset(s->diag, 0, D_COUNT * 8));
+    const tr_image* imgs[4] = {&d->texture, &d->normal_map, &d->normal_map_tangent, &d->specular_map};
+    for (int k = 0; k < 4; ++k) if ((rc = upload_map(s, k, *imgs[k]))) return rc;
+    CU(cudaEventCreate(&s->ev_begin));
+    CU(cudaEventCreate(&s->ev_end));
+    if ((rc = reset_to_new(s))) return rc;
+    CU(cudaStreamSynchronize(s->stream));
+    return TR_OK;
+}
+
+void destroy_impl(tr_scene* s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    for (auto& sp : s->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+    for (auto e : s->event_pool) cudaEventDestroy(e);
+    if (s->ev_begin) cudaEventDestroy(s->ev_begin);
+    if (s->ev_end) cudaEventDestroy(s->ev_end);
+    for (int k = 0; k < 4; ++k) {
+        if (s->maps.tex[k]) cudaDestroyTextureObject(s->maps.tex[k]);
+        if (s->arrays[k]) cudaFreeArray(s->arrays[k]);
+    }
+    for (auto p : s->keys) cudaFree(p);
+    for (auto p : s->rgb) cudaFree(p);
+    cudaFree(s->geom); cudaFree(s->cam.rec); cudaFree(s->cam.var); cudaFree(s->cam.bbox);
+    cudaFree(s->lit.rec); cudaFree(s->lit.bbox);
+    cudaFree(s->shadow); cudaFree(s->ao); cudaFree(s->diag); cudaFree(s->d_checksums); cudaFree(s->scratch);
+    if (s->own_stream) cudaStreamDestroy(s->own_stream);
+    delete s;
+}
+
+// ---- pass issue ------------------------------------------------------------------------------------------
+
+int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
+    if (s->n_tri == 0) return TR_OK;
+    Scoped sp(s, KS_SETUP);
+    dim3 grid((s->n_tri + 127) / 128);
+    if (light_pass) k_vertex_setup<true><<<grid, 128, 0, s->stream>>>(s->geom, s->lit, u, s->pipeline, s->diag);
+    else k_vertex_setup<false><<<grid, 128, 0, s->stream>>>(s->geom, s->cam, u, s->pipeline, s->diag);
+    return launch_ok("k_vertex_setup");
+}
+
+int run_raster(tr_scene* s, bool depth_only, uint32_t epoch, bool fresh) {
+    RasterArgs a{};
+    a.rec = depth_only ? s->lit.rec : s->cam.rec;
+    a.bbox = depth_only ? s->lit.bbox : s->cam.bbox;
+    a.n_triangles = s->n_tri; a.width = s->width; a.height = s->height;
+    a.epoch = epoch; a.fresh = fresh ? 1 : 0;
+    a.keys = s->keys[s->cur]; a.depth = s->shadow; a.diag = s->diag;
+    dim3 grid((s->width + kTileW - 1) / kTileW, (s->height + kTileH - 1) / kTileH);
+    Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
+    if (depth_only) k_raster<true><<<grid, kRasterThreads, 0, s->stream>>>(a);
+    else k_raster<false><<<grid, kRasterThreads, 0, s->stream>>>(a);
+    return launch_ok("k_raster");
+}
+
+template <bool ACCUM>
+int run_shade(tr_scene* s, const Uniforms& u, bool fresh_rgb) {
+    ShadeArgs a{};
+    a.keys = s->keys[s->cur]; a.rec = s->cam.rec; a.var = s->cam.var; a.shadow = s->shadow;
+    a.rgb = s->rgb[s->cur]; a.ao_accum = s->ao; a.diag = s->diag; a.maps = s->maps; a.fresh = fresh_rgb ? 1 : 0;
+    size_t groups = (size_t)((s->width + 3) / 4) * s->height;
+    dim3 grid((unsigned)((groups + 255) / 256));
+    Scoped sp(s, ACCUM ? KS_AO : KS_SHADE);
+    if (ACCUM) { k_shade<P_OCCLUSION, true><<<grid, 256, 0, s->stream>>>(a, u); return launch_ok("k_shade<occlusion,accum>"); }
+    switch (s->pipeline) {
+        case P_DEFAULT: k_shade<P_DEFAULT, false><<<grid, 256, 0, s->stream>>>(a, u); break;
+        case P_PHONG: k_shade<P_PHONG, false><<<grid, 256, 0, s->stream>>>(a, u); break;
+        case P_NORMAL_MAP: k_shade<P_NORMAL_MAP, false><<<grid, 256, 0, s->stream>>>(a, u); break;
+        case P_SPECULAR: k_shade<P_SPECULAR, false><<<grid, 256, 0, s->stream>>>(a, u); break;
+        case P_DARBOUX: k_shade<P_DARBOUX, false><<<grid, 256, 0, s->stream>>>(a, u); break;
+        case P_SHADOW: k_shade<P_SHADOW, false><<<grid, 256, 0, s->stream>>>(a, u); break;
+        default: k_shade<P_OCCLUSION, false><<<grid, 256, 0, s->stream>>>(a, u); break;
+    }
+    return launch_ok("k_shade");
+}
+
+// Scene::render (scene.rs:151-268): every pass = prepare, all polygons through the vertex stage, raster.
+int render_impl(tr_scene* s) {
+    CU(cudaSetDevice(s->device));
+    if (s->epoch > kMaxEpoch) return fail(TR_ERR_UNSUPPORTED, "more than %u renders without tr_scene_clear", kMaxEpoch);
+    int rc;
+    Uniforms u{};
+    u.n_triangles = s->n_tri; u.epoch = s->epoch;
+    if (two_pass(s->pipeline)) {
+        if ((rc = prep_error(prepare_light(u, s->width, s->height, s->light, s->at, s->up)))) return rc;
+        u.n_triangles = s->n_tri; u.epoch = s->epoch;
+        if ((rc = run_setup(s, u, true))) return rc;
+        if ((rc = run_raster(s, true, s->epoch, s->fresh_shadow))) return rc;
+        s->fresh_shadow = false;
+        if ((rc = prep_error(prepare_camera_with_shadow(u, s->width, s->height, s->light, s->from, s->at, s->up, s->pipeline == P_OCCLUSION)))) return rc;
+    } else {
+        if ((rc = prep_error(prepare_camera(u, s->width, s->height, s->light, s->from, s->at, s->up)))) return rc;
+    }
+    if ((rc = run_setup(s, u, false))) return rc;
+    if ((rc = run_raster(s, false, s->epoch, s->fresh_keys))) return rc;
+    s->fresh_keys = false;
+    if ((rc = run_shade<false>(s, u, s->fresh_rgb))) return rc;
+    s->fresh_rgb = false;
+    s->uni = u;
+    s->epoch++;
+    return TR_OK;
+}
+
+int checksum_into(tr_scene* s, const uint8_t* img, size_t n_bytes, unsigned long long* d_out) {
+    CU(cudaMemsetAsync(d_out, 0, 8, s->stream));
+    Scoped sp(s, KS_CHECKSUM);
+    k_checksum<<<148 * 4, 256, 0, s->stream>>>(reinterpret_cast<const uint32_t*>(img), n_bytes / 4, d_out);
+    return launch_ok("k_checksum");
+}
+
+}  // namespace
+
+// ============================================ C ABI ==========================================================
+#define NEED(s) do { if (!(s)) return fail(TR_ERR_INVALID_ARGUMENT, "%s: null scene", __func__); clear_error(); } while (0)
+
+extern "C" {
+
+const char* tr_last_error(void) { return last_error(); }
+const char* tr_version(void) { return TR_VERSION_STRING; }
+
+int tr_device_count(int* n) {
+    if (!n) return fail(TR_ERR_INVALID_ARGUMENT, "null argument");
+    *n = 0;
+    if (cudaGetDeviceCount(n) != cudaSuccess) { cudaGetLastError(); *n = 0; return fail(TR_ERR_NO_DEVICE, "no CUDA device"); }
+    return TR_OK;
+}
+
+int tr_scene_create(tr_scene** out, const tr_scene_desc* desc) {
+    if (!out || !desc) return fail(TR_ERR_INVALID_ARGUMENT, "tr_scene_create: null argument");
+    *out = nullptr;
+    clear_error();
+    tr_scene* s = new tr_scene();
+    int rc = create_impl(s, desc);
+    if (rc) { std::string keep = last_error(); destroy_impl(s); fail(rc, "%s", keep.c_str()); return rc; }
+    *out = s;
+    return TR_OK;
+}
+
+void tr_scene_destroy(tr_scene* s) { destroy_impl(s); }
+
+// Scene::clear (scene.rs:128-137).  Lazy: the z/shadow/frame fills are folded into the tile initialisation of
+// the next render; getters called before that materialise them.
+int tr_scene_clear(tr_scene* s) {
+    NEED(s);
+    s->fresh_keys = s->fresh_rgb = s->fresh_shadow = true;
+    s->epoch = 0;
+    return TR_OK;
+}
+
+int tr_scene_set_light_direction(tr_scene* s, const float d[3]) {
+    NEED(s);
+    if (!d) return fail(TR_ERR_INVALID_ARGUMENT, "null direction");
+    s->light = {d[0], d[1], d[2]};
+    return TR_OK;
+}
+
+int tr_scene_set_camera(tr_scene* s, const float from[3], const float at[3], const float up[3]) {
+    NEED(s);
+    if (!from || !at || !up) return fail(TR_ERR_INVALID_ARGUMENT, "null camera vector");
+    s->from = {from[0], from[1], from[2]}; s->at = {at[0], at[1], at[2]}; s->up = {up[0], up[1], up[2]};
+    return TR_OK;
+}
+
+int tr_scene_render(tr_scene* s) { NEED(s); return render_impl(s); }
+
+int tr_scene_synchronize(tr_scene* s) {
+    NEED(s);
+    CU(cudaSetDevice(s->device));
+    CU(cudaStreamSynchronize(s->stream));
+    return TR_OK;
+}
+
+int tr_scene_set_pipeline(tr_scene* s, const char* name) {
+    NEED(s);
+    int p = pipeline_from_name(name);
+    if (p < 0) return fail(TR_ERR_UNKNOWN_PIPELINE, "Provided pipeline name is not supported! (%s)", name ? name : "null");
+    CU(cudaSetDevice(s->device));
+    s->pipeline = p;
+    return reset_to_new(s);
+}
+
+int tr_scene_set_stream(tr_scene* s, void* stream) {
+    NEED(s);
+    CU(cudaSetDevice(s->device));
+    CU(cudaStreamSynchronize(s->stream));
+    s->stream = stream ? (cudaStream_t)stream : s->own_stream;
+    return TR_OK;
+}
+
+// get_frame_buffer (scene.rs:92-97): frames are stored top-down on the device, so this is one D2H copy.
+int tr_scene_get_frame_buffer(tr_scene* s, uint8_t* dst) {
+    NEED(s);
+    if (!dst) return fail(TR_ERR_INVALID_ARGUMENT, "null destination");
+    CU(cudaSetDevice(s->device));
+    int rc = materialise(s);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(dst, s->rgb[s->cur], s->n_px * 3, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return TR_OK;
+}
+
+int tr_scene_read_frame_raw(tr_scene* s, uint8_t* dst) {
+    NEED(s);
+    if (!dst) return fail(TR_ERR_INVALID_ARGUMENT, "null destination");
+    CU(cudaSetDevice(s->device));
+    int rc = materialise(s);
+    if (rc) return rc;
+    if ((rc = ensure_scratch(s, s->n_px * 3))) return rc;
+    size_t n = s->n_px * 3;
+    k_flip_rows<<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(s->rgb[s->cur], s->scratch, s->width * 3, s->height);
+    if ((rc = launch_ok("k_flip_rows"))) return rc;
+    CU(cudaMemcpyAsync(dst, s->scratch, n, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return TR_OK;
+}
+
+static int gray_view(tr_scene* s, uint8_t* dst, bool shadow) {
+    if (!dst) return fail(TR_ERR_INVALID_ARGUMENT, "null destination");
+    CU(cudaSetDevice(s->device));
+    int rc = materialise(s);
+    if (rc) return rc;
+    if ((rc = ensure_scratch(s, s->n_px * 3))) return rc;
+    k_gray_view<<<(unsigned)((s->n_px + 255) / 256), 256, 0, s->stream>>>(shadow ? nullptr : s->keys[s->cur], s->shadow, s->scratch, s->width, s->height);
+    if ((rc = launch_ok("k_gray_view"))) return rc;
+    CU(cudaMemcpyAsync(dst, s->scratch, s->n_px * 3, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return TR_OK;
+}
+int tr_scene_get_z_buffer(tr_scene* s, uint8_t* dst) { NEED(s); return gray_view(s, dst, false); }
+int tr_scene_get_shadow_buffer(tr_scene* s, uint8_t* dst) { NEED(s); return gray_view(s, dst, true); }
+
+static int read_unpacked(tr_scene* s, float* depth, uint32_t* tri) {
+    CU(cudaSetDevice(s->device));
+    int rc = materialise(s);
+    if (rc) return rc;
+    if ((rc = ensure_scratch(s, s->n_px * 4))) return rc;
+    k_unpack_keys<<<(unsigned)((s->n_px + 255) / 256), 256, 0, s->stream>>>(s->keys[s->cur], depth ? (float*)s->scratch : nullptr,
+                                                                         tri ? (uint32_t*)s->scratch : nullptr, s->n_px);
+    if ((rc = launch_ok("k_unpack_keys"))) return rc;
+    CU(cudaMemcpyAsync(depth ? (void*)depth : (void*)tri, s->scratch, s->n_px * 4, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return TR_OK;
+}
+int tr_scene_read_depth(tr_scene* s, float* dst) { NEED(s); if (!dst) return fail(TR_ERR_INVALID_ARGUMENT, "null destination"); return read_unpacked(s, dst, nullptr); }
+int tr_scene_read_visibility(tr_scene* s, uint32_t* dst) { NEED(s); if (!dst) return fail(TR_ERR_INVALID_ARGUMENT, "null destination"); return read_unpacked(s, nullptr, dst); }
+
+int tr_scene_read_shadow(tr_scene* s, float* dst) {
+    NEED(s);
+    if (!dst) return fail(TR_ERR_INVALID_ARGUMENT, "null destination");
+    CU(cudaSetDevice(s->device));
+    int rc = materialise(s);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(dst, s->shadow, s->n_px * 4, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return TR_OK;
+}
+
+int tr_scene_diagnostics(tr_scene* s, uint64_t out[8]) {
+    NEED(s);
+    if (!out) return fail(TR_ERR_INVALID_ARGUMENT, "null destination");
+    CU(cudaSetDevice(s->device));
+    CU(cudaMemcpyAsync(out, s->diag, D_COUNT * 8, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return TR_OK;
+}
+
+int tr_scene_get_uniforms(tr_scene* s, float out[102]) {
+    NEED(s);
+    if (!out) return fail(TR_ERR_INVALID_ARGUMENT, "null destination");
+    const mat4* ms[6] = {&s->uni.vpmv, &s->uni.i_vpmv, &s->uni.m, &s->uni.i_m, &s->uni.it_m, &s->uni.shadow};
+    for (int k = 0; k < 6; ++k) memcpy(out + 16 * k, ms[k]->m, 64);
+    out[96] = s->uni.camera_direction.x; out[97] = s->uni.camera_direction.y; out[98] = s->uni.camera_direction.z;
+    out[99] = s->uni.t_light.x; out[100] = s->uni.t_light.y; out[101] = s->uni.t_light.z;
+    return TR_OK;
+}
+
+int tr_scene_device_frame(tr_scene* s, void** p) {
+    NEED(s);
+    if (!p) return fail(TR_ERR_INVALID_ARGUMENT, "null destination");
+    CU(cudaSetDevice(s->device));
+    int rc = materialise(s);
+    *p = s->rgb[s->cur];
+    return rc;
+}
+
+}  // extern "C"
+
+#include "tinyr_batch.inc"
