@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 rasterization backend (contract: see the task statement).
+
+    python bench.py --gpus 1 --steps K --warmup W            # own arm
+    python bench.py --impl reference --gpus 1 --steps K ...  # the reference's CPU path (oracle port) on host cores
+    torchrun ... bench.py --gpus N ...                       # one rank per GPU, weak scaling over view batches
+
+Metric (BASELINE.json): Mpixels/s shaded, device-timed, at 3840x2160.  Workload at every N = BASELINE config 2:
+diablo, phong + darboux, 3840x2160, 8 camera angles 2*pi*k/8, light angle 0.7 rad -> one step = 16 frames per
+GPU, each `clear; set_light_direction; set_camera; render` (app.rs:170,208-210).  N > 1 shards independent view
+batches (no data-path collective) and additionally reports the many-light AO mode (config 4: lights sharded,
+one NCCL all-reduce of the u32 accumulators) under "ao".
+"""
+import argparse
+import json
+import math
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+W4K, H4K = 3840, 2160
+PIPES = ("phong", "darboux")
+N_ANGLES = 8
+LIGHT_ANGLE = 0.7
+RING = 4   # 4 x (8 B keys + 3 B rgb) x 8.29 Mpx = 365 MB of render targets > 126 MB L2
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def bench_model():
+    import assets
+    m = assets.get_model("diablo")
+    data = "reference asset diablo (staged copy of /root/reference/assets), synthetic views" if m.name == "diablo" \
+        else "synthetic procedural model (reference assets not staged), synthetic views"
+    return m, data
+
+
+def view_batch(rank=0):
+    """8 camera angles (rank offsets the phase so ranks do not render identical frames), app.rs:200-207."""
+    import assets
+    v = np.zeros((N_ANGLES, 12), np.float32)
+    for k in range(N_ANGLES):
+        lf, la, up, light = assets.view_vectors(2 * math.pi * k / N_ANGLES + 0.01 * rank, LIGHT_ANGLE)
+        v[k, 0:3], v[k, 3:6], v[k, 6:9], v[k, 9:12] = lf, la, up, light
+    return v
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (recipe in B200_PROFILING.md)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ---- CPU side: the reference's own CPU path, as restated by the oracle (Rust cannot be compiled here) --------
+
+def cpu_render_frames(model, jobs, threads):
+    """jobs: list of (pipeline, view_row).  Each worker owns its OracleScenes (ctypes releases the GIL)."""
+    import oracle_lib
+    lock, pos = threading.Lock(), [0]
+
+    def worker():
+        scenes = {}
+        while True:
+            with lock:
+                i = pos[0]
+                pos[0] += 1
+            if i >= len(jobs):
+                return
+            pipe, v = jobs[i]
+            s = scenes.get(pipe)
+            if s is None:
+                s = scenes[pipe] = oracle_lib.OracleScene(W4K, H4K, model, pipe)
+            s.clear(); s.set_light_direction(v[9:12]); s.set_camera(v[0:3], v[3:6], v[6:9]); s.render()
+            s.get_frame_buffer()
+
+    # scene construction (buffer allocation) happens inside the timed region for the first job of each worker;
+    # it is ~10 ms against >= 300 ms per 4K frame.
+    t0 = time.perf_counter()
+    ts = [threading.Thread(target=worker) for _ in range(threads)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    return time.perf_counter() - t0
+
+
+def cpu_baseline(model, n_frames_per_pipe=2):
+    """Faithful single-thread baseline (the reference's render loop is single-threaded, scene.rs:151) on a
+    bounded sample of the same workload: n views of each pipeline at 3840x2160."""
+    views = view_batch()
+    jobs = [(p, views[k]) for p in PIPES for k in range(n_frames_per_pipe)]
+    secs = cpu_render_frames(model, jobs, 1)
+    return {"value": len(jobs) * W4K * H4K / secs / 1e6, "unit": "Mpixels/s", "cores": 1, "kind": "port",
+            "sample": "%d frames (%d views x phong+darboux) at 3840x2160, oracle C++ port of scene.rs/shader.rs, 1 thread, %.2f s"
+                      % (len(jobs), n_frames_per_pipe, secs)}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path (the oracle port — the Rust crate cannot
+    be built on this box) on all host threads it can use, same config/metric/unit."""
+    if rank != 0:
+        return
+    model, data = bench_model()
+    cores = os.cpu_count() or 1
+    views = view_batch()
+    jobs = [(p, views[k]) for p in PIPES for k in range(N_ANGLES)]       # one full step = 16 frames
+    threads = min(cores, len(jobs))
+    times = []
+    for i in range(args.warmup + args.steps):
+        t = cpu_render_frames(model, jobs, threads)
+        if i >= args.warmup:
+            times.append(t)
+    total = sum(times)
+    value = args.steps * len(jobs) * W4K * H4K / total / 1e6
+    line = {"impl": "reference", "metric": "Mpixels/s shaded at 3840x2160", "value": value, "unit": "Mpixels/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": data,
+            "config": workload_config(),
+            "cpu_baseline": {"value": value, "unit": "Mpixels/s", "cores": threads, "kind": "port",
+                             "sample": "full step: 16 frames at 3840x2160 per step over %d host threads" % threads},
+            "e2e": {"value": value, "unit": "Mpixels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config():
+    return {"workload": "BASELINE config 2: diablo, phong + darboux, 3840x2160, 8 camera angles 2*pi*k/8, light 0.7 rad "
+                        "(16 frames per step per GPU)", "width": W4K, "height": H4K, "frames_per_step_per_gpu": len(PIPES) * N_ANGLES,
+            "triangles": 5022, "l2": "render targets rotate through a ring of %d buffer sets (365 MB > 126 MB L2)" % RING,
+            "parallelism": "independent view batches per GPU, no data-path collective"}
+
+
+# ---- GPU arm -----------------------------------------------------------------------------------------------
+
+def algorithmic_bytes(n_px, covered, n_tri, pipe):
+    """SURVEY.md §8(d) / BASELINE.md §3: B_frame = 19*P + n_maps*min(3*C, 3 MiB) + geometry, split per kernel.
+    K3 raster: key write 8*P + setup records (64 B) and bboxes (16 B) read once.
+    K5 shade : key read 8*P + RGB write 3*P + compulsory texels + records/varyings of the drawn polygons."""
+    n_maps = {"phong": 1, "darboux": 2}[pipe]
+    tex = n_maps * min(3 * covered, 3 << 20)
+    k1 = n_tri * (96 + 64 + 16 + (96 if pipe == "darboux" else 16))
+    k3 = 8 * n_px + n_tri * (64 + 16)
+    k5 = 8 * n_px + 3 * n_px + tex + n_tri * (64 + 96)
+    return {"K1_vertex_setup": k1, "K3_raster_visibility": k3, "K5_shade": k5, "frame": 19 * n_px + tex + k1}
+
+
+def run_gpu(args, rank, world, local_rank):
+    import torch
+    import tiny_renderer_b200 as tr
+    from tiny_renderer_b200.scene import Scene
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = local_rank
+    torch.cuda.set_device(dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    model, data = bench_model()
+    n_px = W4K * H4K
+    n_tri = len(model.tri_idx)
+    views = view_batch(rank)
+    scenes = {p: Scene(W4K, H4K, model, p, device=dev, ring=RING) for p in PIPES}
+    for s in scenes.values():
+        s.set_stream(stream)
+
+    def step():
+        for p in PIPES:
+            scenes[p].render_views(views, want_checksums=False)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    for s in scenes.values():
+        s.kernel_times()                      # reset launch counters
+    sampler = ClockSampler(dev)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = sum(n for s in scenes.values() for (_, n) in s.kernel_times().values())
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    frames_per_step = len(PIPES) * N_ANGLES
+    value = world * args.steps * frames_per_step * n_px / (ms * 1e-3) / 1e6
+
+    # ---- e2e: the reference-facing calls with a HOST destination, D2H inside the timed region ----
+    host = tr.pinned_empty((H4K, W4K, 3), np.uint8)
+    def e2e_step():
+        for p in PIPES:
+            s = scenes[p]
+            for v in views:
+                s.clear(); s.set_light_direction(v[9:12]); s.set_camera(v[0:3], v[3:6], v[6:9]); s.render()
+                s.get_frame_buffer(out=host)
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(1, min(args.steps, 3))
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = world * e2e_steps * frames_per_step * n_px / e2e_s / 1e6
+
+    line = {"metric": "Mpixels/s shaded (device-timed) at 3840x2160", "value": value, "unit": "Mpixels/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": data, "config": workload_config(),
+            "e2e": {"value": e2e_value, "unit": "Mpixels/s", "h2d_bytes_per_step": frames_per_step * 48,
+                    "d2h_bytes_per_step": frames_per_step * n_px * 3,
+                    "note": "clear/set_light_direction/set_camera/render/get_frame_buffer per frame into pinned host memory; "
+                            "inputs are the 12 floats of camera+light per frame (kernel arguments)"},
+            "gpu_launches": int(launches), "clocks": clocks}
+
+    if rank == 0:
+        # ---- roofline of the dominant kernel: per-kernel CUDA events (profiling mode), separate from `value` ----
+        peak, peak_src = load_peaks()
+        per = {}
+        covered = {}
+        for p in PIPES:
+            s = scenes[p]
+            s.set_profiling(True)
+            s.kernel_times()
+            for _ in range(3):
+                s.render_views(views, want_checksums=False)
+            kt = s.kernel_times()
+            s.set_profiling(False)
+            covered[p] = int((s.raw_visibility() != 0xFFFFFFFF).sum())
+            per[p] = {k: (t / n * 1e3 if n else 0.0) for k, (t, n) in kt.items() if n}     # us per launch
+        line["kernel_us"] = per
+        best = None
+        for p in PIPES:
+            ab = algorithmic_bytes(n_px, covered[p], n_tri, p)
+            frame_us = sum(per[p].get(k, 0.0) for k in ("K1_vertex_setup", "K3_raster_visibility", "K5_shade"))
+            for k in ("K3_raster_visibility", "K5_shade"):
+                us = per[p].get(k, 0.0)
+                if best is None or us > best[0]:
+                    best = (us, p, k, ab[k], ab["frame"], frame_us)
+        us, p, k, nbytes, frame_bytes, frame_us = best
+        achieved = nbytes / (us * 1e-6) / 1e9
+        line["roofline"] = {"bound": "hbm", "kernel": "%s (%s)" % (k, p), "achieved": achieved, "peak": peak, "unit": "GB/s",
+                            "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                            "algorithmic_bytes_per_launch": nbytes, "us_per_launch": us,
+                            "frame": {"algorithmic_bytes": frame_bytes, "us": frame_us,
+                                      "achieved": frame_bytes / (frame_us * 1e-6) / 1e9,
+                                      "frac": frame_bytes / (frame_us * 1e-6) / 1e9 / peak}}
+        if world == 1:
+            line["cpu_baseline"] = cpu_baseline(model)
+    for s in scenes.values():
+        s.close()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="tinyr", choices=["tinyr", "reference"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    run_gpu(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()
