@@ -1,9 +1,10 @@
-// k_setup.cuh — K1 vertex_setup: one thread per polygon, coalesced float4 loads of the corner-expanded
+// k_setup.cuh — K1 vertex_setup (+ K2 bin, fused): one thread per polygon, coalesced float4 loads of the corner-expanded
 // static geometry, SoA setup records out.  Replaces the reference's vertex closures
 // (/root/reference/src/scene/shader.rs:285-316, 349-384, 416-437, 475-496, 549-595, 671-692, 711-747,
 // 809-830, 849-870), their helpers (shader.rs:116-165) and the bounding box of scene.rs:232-239.
 #pragma once
 #include "tr_types.cuh"
+#include "k_raster.cuh"
 
 namespace tr {
 
@@ -15,6 +16,7 @@ struct SetupOut {
     float4* rec;      // n_triangles x 4 float4 (kRecWords)
     float4* var;      // n_triangles x 6 float4 (kVarWords), may be null when the pipeline needs none
     int4* bbox;       // n_triangles: xmin ymin xmax ymax clamped to the screen; xmin > xmax when not drawn
+    Bins bins;        // K2: per-tile polygon lists for the raster kernel that follows
 };
 
 // it_m * (n, 0) -> must have w == 0 -> normalised   (shader.rs:300-303, 368-371)
@@ -29,7 +31,8 @@ template <bool LIGHT_PASS>
 __global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__ geom, SetupOut out, const Uniforms u,
                                                      int pipeline, unsigned long long* diag) {
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= u.n_triangles) return;
+    const bool valid = t < u.n_triangles;        // no early return: the whole warp takes part in the binning
+    if (!valid) t = u.n_triangles - 1;
     float g[kStaticWords];
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
@@ -52,7 +55,7 @@ __global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__
     for (int i = 0; i < 3; ++i) {
         bool ok;
         f3 s = dehomog(xform(M, f4{p[i].x, p[i].y, p[i].z, 1.0f}), ok);
-        if (!ok && drawn) atomicAdd(&diag[D_W_ZERO], 1ull);
+        if (!ok && drawn && valid) atomicAdd(&diag[D_W_ZERO], 1ull);
         rx[i] = cast_i32(s.x);
         ry[i] = cast_i32(s.y);
         rz[i] = s.z;
@@ -61,8 +64,47 @@ __global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__
     int32_t xmin = max(0, min(min(rx[0], rx[1]), rx[2])), xmax = min(max(max(rx[0], rx[1]), rx[2]), (int32_t)u.width - 1);
     int32_t ymin = max(0, min(min(ry[0], ry[1]), ry[2])), ymax = min(max(max(ry[0], ry[1]), ry[2]), (int32_t)u.height - 1);
     if (!drawn || ymin > ymax) { xmin = 1; xmax = 0; }
-    out.bbox[t] = make_int4(xmin, ymin, xmax, ymax);
+    if (valid) out.bbox[t] = make_int4(xmin, ymin, xmax, ymax);
+    // K2 bin (fused): append the polygon to every screen tile its clamped bounding box touches.  The order inside
+    // a bin is whatever the atomics give; visibility does not depend on it (packed-key min is commutative).
+    // The warp walks its 32 polygons one after the other with the lanes spread over the polygon's tiles, so a
+    // polygon covering dozens of tiles costs one round of independent atomics instead of a serial chain.
+    {
+        const bool any = valid && xmin <= xmax;
+        const int bx0 = any ? xmin / kTileW : 0, by0 = any ? ymin / kTileH : 0;
+        const int nx = any ? xmax / kTileW - bx0 + 1 : 0, ny = any ? ymax / kTileH - by0 + 1 : 0;
+        const int lane = threadIdx.x & 31;
+        const unsigned peers = 0xffffffffu;
+        // Small footprints (<= 4 tiles, the common case): the owning thread issues its atomics back to back.
+        const bool small = any && nx * ny <= 4;
+        if (small) {
+            uint32_t tl[4], sl[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                tl[i] = (uint32_t)(by0 + i / nx) * out.bins.tiles_x + (uint32_t)(bx0 + i % nx);
+                sl[i] = kBinCap;
+                if (i < nx * ny) sl[i] = atomicAdd(&out.bins.count[tl[i]], 1u);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (sl[i] < (uint32_t)kBinCap) out.bins.list[(size_t)tl[i] * kBinCap + sl[i]] = t;
+        }
+        unsigned todo = __ballot_sync(peers, any && !small);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int sbx0 = __shfl_sync(peers, bx0, src), sby0 = __shfl_sync(peers, by0, src);
+            const int snx = __shfl_sync(peers, nx, src), sny = __shfl_sync(peers, ny, src);
+            const uint32_t st = __shfl_sync(peers, t, src);
+            for (int i = lane; i < snx * sny; i += 32) {
+                uint32_t tile = (uint32_t)(sby0 + i / snx) * out.bins.tiles_x + (uint32_t)(sbx0 + i % snx);
+                uint32_t slot = atomicAdd(&out.bins.count[tile], 1u);
+                if (slot < (uint32_t)kBinCap) out.bins.list[(size_t)tile * kBinCap + slot] = st;
+            }
+        }
+    }
 
+    if (!valid) return;
     float4* rec = out.rec + (size_t)t * 4;
     rec[0] = make_float4(__int_as_float(rx[0]), __int_as_float(ry[0]), __int_as_float(rx[1]), __int_as_float(ry[1]));
     rec[1] = make_float4(__int_as_float(rx[2]), __int_as_float(ry[2]), rz[0], rz[1]);

@@ -45,6 +45,7 @@ struct tr_scene {
     float* shadow = nullptr;
     uint32_t* ao = nullptr;
     unsigned long long* diag = nullptr;
+    Bins bins{};
     unsigned long long* d_checksums = nullptr; size_t checksum_cap = 0;
     uint8_t* scratch = nullptr; size_t scratch_bytes = 0;
     cudaArray_t arrays[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -208,6 +209,14 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
     int rc;
     if ((rc = alloc_setup(&s->cam, s->n_tri, true))) return rc;
     if ((rc = alloc_setup(&s->lit, s->n_tri, false))) return rc;
+    s->bins.tiles_x = (s->width + kTileW - 1) / kTileW;
+    s->bins.tiles_y = (s->height + kTileH - 1) / kTileH;
+    const size_t n_tiles = (size_t)s->bins.tiles_x * s->bins.tiles_y;
+    CU(cudaMalloc(&s->bins.count, n_tiles * 4));
+    CU(cudaMemset(s->bins.count, 0, n_tiles * 4));
+    CU(cudaMalloc(&s->bins.list, n_tiles * kBinCap * 4));
+    s->cam.bins = s->bins;
+    s->lit.bins = s->bins;
     s->keys.assign(s->ring, nullptr); s->rgb.assign(s->ring, nullptr);
     for (uint32_t r = 0; r < s->ring; ++r) {
         CU(cudaMalloc(&s->keys[r], s->n_px * 8));
@@ -243,6 +252,7 @@ void destroy_impl(tr_scene* s) {
     for (auto p : s->rgb) cudaFree(p);
     cudaFree(s->geom); cudaFree(s->cam.rec); cudaFree(s->cam.var); cudaFree(s->cam.bbox);
     cudaFree(s->lit.rec); cudaFree(s->lit.bbox);
+    cudaFree(s->bins.count); cudaFree(s->bins.list);
     cudaFree(s->shadow); cudaFree(s->ao); cudaFree(s->diag); cudaFree(s->d_checksums); cudaFree(s->scratch);
     if (s->own_stream) cudaStreamDestroy(s->own_stream);
     delete s;
@@ -263,6 +273,7 @@ int run_raster(tr_scene* s, bool depth_only, uint32_t epoch, bool fresh) {
     RasterArgs a{};
     a.rec = depth_only ? s->lit.rec : s->cam.rec;
     a.bbox = depth_only ? s->lit.bbox : s->cam.bbox;
+    a.bins = s->bins;
     a.n_triangles = s->n_tri; a.width = s->width; a.height = s->height;
     a.epoch = epoch; a.fresh = fresh ? 1 : 0;
     a.keys = s->keys[s->cur]; a.depth = s->shadow; a.diag = s->diag;
