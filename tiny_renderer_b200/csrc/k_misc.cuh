@@ -1,6 +1,6 @@
 // k_misc.cuh — K7 clear / views / flips and K8 frame checksum.
 #pragma once
-#include "tr_types.cuh"
+#include "k_tile.cuh"
 
 namespace tr {
 
@@ -13,6 +13,20 @@ __global__ void __launch_bounds__(256) k_fill_state(unsigned long long* keys, fl
     if (do_keys) for (size_t i = i0; i < n_px; i += stride) keys[i] = k;
     if (do_shadow) for (size_t i = i0; i < n_px; i += stride) shadow[i] = z_init;
     if (do_rgb) for (size_t i = i0; i < n_rgb_words; i += stride) rgb_words[i] = 0u;
+}
+
+// Writes the cleared key into every tile still in the tile-level cleared state (k_raster.cuh) and marks it as
+// materialised; getters that read key memory call this first.  One CTA per raster tile.
+__global__ void __launch_bounds__(256) k_materialise_tiles(unsigned long long* keys, uint32_t* tile_state, uint32_t width, uint32_t height) {
+    const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
+    if (tile_state[tile] == 0u) return;
+    const unsigned long long k = make_key(-3.402823466e38f, kNoTri);
+    for (int i = threadIdx.x; i < kTileW * kTileH; i += 256) {
+        uint32_t px = blockIdx.x * kTileW + i % kTileW, py = blockIdx.y * kTileH + i / kTileW;
+        if (px < width && py < height) keys[(size_t)py * width + px] = k;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) tile_state[tile] = 0u;
 }
 
 // Raw bottom-up views of the state the reference keeps in Buffer.z_buffer / visibility (derived from keys).

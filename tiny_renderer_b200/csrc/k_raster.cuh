@@ -1,12 +1,15 @@
-// k_raster.cuh — K3 raster_visibility / K4 shadow_depth: sort-middle tile rasteriser.
+// k_raster.cuh — K3 raster_visibility (+ K5 shading, fused) / K4 shadow_depth: sort-middle tile rasteriser.
 //
-// One CTA owns one kTileW x kTileH screen tile.  (1) It takes the tile's polygon list from the bins K1+K2 filled
-// (falling back to a scan of all bounding boxes when a bin overflowed) and stages per-polygon edge equations in
-// shared memory.  (2) Each warp owns 8x4-pixel blocks of the tile, one pixel per lane: 32 lanes test 32 staged
-// bounding boxes against the block, a ballot yields the candidate mask, and every lane evaluates the inside test
-// for its own pixel with operands broadcast from shared memory.  Visibility is resolved in registers as a 64-bit
-// min over packed (depth, epoch|polygon) keys — the order a global 64-bit atomicMin would give, without the L2
-// round trips — and each tile is written once, coalesced.  Tiles no polygon touches only write the cleared value.
+// One CTA owns one kTileW x kTileH screen tile.  (1) It filters the polygon list of the binning cell the tile lies
+// in (K1+K2; a scan of all bounding boxes when the cell's bin overflowed) against the tile and stages per-polygon
+// edge equations in shared memory.  (2) Warps pull 8x4-pixel blocks off the tile, one pixel per lane: 32 lanes test
+// 32 staged bounding boxes against the block, a ballot yields the candidate mask, and every lane evaluates the
+// inside test for its own pixel with operands broadcast from shared memory.  Visibility is resolved in registers —
+// (depth, epoch|polygon) compared the way a 64-bit atomicMin on the packed key would order them, without the L2
+// round trips — and the key of every pixel of a touched tile is written once.  (3) In the shading modes the lane
+// then runs the pipeline's fragment math for its winner (k_shade.cuh) with the barycentrics it already holds,
+// the tile's RGB is collected in shared memory and stored with 16-byte writes.  Tiles no polygon touches cost one
+// word of tile state (see RasterArgs::tile_state) plus, when shading, their zeroed RGB.
 //
 // Arithmetic: the reference evaluates, per pixel, c = u x v in f32 and bar = (1-(cx+cy)/cz, cx/cz, cy/cz)
 // (/root/reference/src/scene.rs:174-197), rejects bar.* < 0 (:245) and takes z = bar . z (shader.rs:174).  When
@@ -15,26 +18,17 @@
 // here (proof in DESIGN.md §K3); the divisions and z are then done in f32 exactly as the reference does, for
 // inside pixels only.  Larger polygons take the literal f32 path (fragment_depth).
 //
-// Replaces scene.rs:232-258 and process_z_value (/root/reference/src/scene/shader.rs:169-180); in DEPTH_ONLY
-// mode the pass-1 fragment shaders of shadow / occlusion (shader.rs:694-709, 832-847).
+// Replaces scene.rs:232-258 and process_z_value (/root/reference/src/scene/shader.rs:169-180) plus the fragment
+// closures (k_shade.cuh); in depth-only mode the pass-1 fragment shaders of shadow / occlusion
+// (shader.rs:694-709, 832-847).
 #pragma once
-#include "tr_types.cuh"
+#include "k_shade.cuh"
 
 namespace tr {
 
-constexpr int kTileW = 64, kTileH = 32;
-constexpr int kRasterThreads = 256;
-constexpr int kListCap = 512;          // staged polygons per round; longer lists are processed in rounds
-constexpr int kBinCap = 256;           // ids per tile bin (K2); a fuller bin makes the tile scan all polygons
-constexpr int kStageWords = 12;        // A1 B1 C1 A2 B2 C2 |cz| id|flag z0 z1 z2 pad   (or raw x0 y0 x1 y1 x2 y2 when inexact)
-constexpr int kExactExtent = 2048;
-constexpr uint32_t kInexactFlag = 0x80000000u;
-
-struct Bins {
-    uint32_t* count;                   // per tile; reset to 0 by the raster kernel that consumes it
-    uint32_t* list;                    // per tile kBinCap polygon ids (unordered)
-    uint32_t tiles_x, tiles_y;
-};
+// Kernel modes: a pipeline id (P_DEFAULT..P_OCCLUSION) = visibility + shading of that pipeline.
+constexpr int kModeDepthOnly = -2;     // K4: shadow buffer, `>=` max, no culling upstream
+constexpr int kModeVisibility = -1;    // K3 alone: keys only (camera pass of the many-light AO batch)
 
 struct RasterArgs {
     const float4* rec;
@@ -42,30 +36,17 @@ struct RasterArgs {
     Bins bins;
     uint32_t n_triangles;
     uint32_t width, height;
+    uint32_t tiles_x;
     uint32_t epoch;
     int fresh;                 // 1: target was cleared (init from constants, scene.rs:128-137), 0: merge with memory
-    unsigned long long* keys;  // visibility mode
-    float* depth;              // DEPTH_ONLY mode (shadow buffer)
+    unsigned long long* keys;  // visibility modes
+    // Visibility modes, per tile: 1 = every pixel of the tile holds the cleared value and the key memory of the tile
+    // is stale.  Scene::clear therefore costs nothing for tiles no polygon touches; K6 and the getters never read
+    // their keys.
+    uint32_t* tile_state;
+    float* depth;              // depth-only mode (shadow buffer)
     unsigned long long* diag;
 };
-
-// The reference's per-pixel arithmetic, literally (scene.rs:178-196, shader.rs:174).  Returns false when the
-// pixel is outside the polygon or the polygon is degenerate.
-__device__ __forceinline__ bool fragment_depth(int x0, int y0, int x1, int y1, int x2, int y2, float z0, float z1, float z2,
-                                               int px, int py, float& z, float& b0, float& b1, float& b2) {
-    float ux = (float)(x1 - x0), uy = (float)(x2 - x0), uz = (float)(x0 - px);
-    float vx = (float)(y1 - y0), vy = (float)(y2 - y0), vz = (float)(y0 - py);
-    float cx = uy * vz - uz * vy;
-    float cy = uz * vx - ux * vz;
-    float cz = ux * vy - uy * vx;
-    if (fabsf(cz) < 1.0f) return false;
-    b0 = 1.0f - (cx + cy) / cz;
-    b1 = cx / cz;
-    b2 = cy / cz;
-    if (b0 < 0.0f || b1 < 0.0f || b2 < 0.0f) return false;
-    z = (b0 * z0 + b1 * z1) + b2 * z2;
-    return true;
-}
 
 // Stage polygon t into slot: edge equations relative to the tile origin, or raw coordinates when inexact.
 __device__ __forceinline__ void stage_polygon(const RasterArgs& a, uint32_t t, int4 bb, int slot, int tx0, int ty0, int tx1, int ty1,
@@ -97,103 +78,91 @@ __device__ __forceinline__ void stage_polygon(const RasterArgs& a, uint32_t t, i
     s_hi[slot] = hi;
 }
 
-template <bool DEPTH_ONLY>
-__global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a) {
+template <int MODE>
+__global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u) {
+    constexpr bool DEPTH_ONLY = MODE == kModeDepthOnly;
+    constexpr bool SHADE = MODE >= 0;
+    constexpr int kRgbRow = kTileW * 3;
     __shared__ __align__(16) float s_tri[kListCap * kStageWords];
     __shared__ int s_lo[kListCap], s_hi[kListCap];
+    __shared__ __align__(16) uint8_t s_rgb[SHADE ? kTileH * kRgbRow : 16];
     __shared__ int s_warp_count[kRasterThreads / 32];
     __shared__ int s_count;
     __shared__ int s_next;
+    __shared__ int s_block;                                 // next 8x4 block of the tile to hand to a warp
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
     const int tx1 = min(tx0 + kTileW, (int)a.width) - 1, ty1 = min(ty0 + kTileH, (int)a.height) - 1;
     const float kFloatMin = -3.402823466e38f;
     constexpr int kBlocksX = kTileW / 8;
-    constexpr int kBlocksPerWarp = kBlocksX * (kTileH / 4) / (kRasterThreads / 32);
+    constexpr int kBlocks = kBlocksX * (kTileH / 4);
 
-    const uint32_t tile = blockIdx.y * a.bins.tiles_x + blockIdx.x;
-    const uint32_t n_bin = a.bins.count[tile];
-    __syncthreads();
-    if (tid == 0) a.bins.count[tile] = 0;                 // self-cleaning: ready for the next K1+K2
-
-    if (n_bin == 0) {
-        // Nothing touches this tile: a cleared target gets the cleared value, an uncleared one keeps its contents.
-        if (!a.fresh) return;
-#pragma unroll
-        for (int b = 0; b < kBlocksPerWarp; ++b) {
-            int blk = warp * kBlocksPerWarp + b;
-            int px = tx0 + (blk % kBlocksX) * 8 + (lane & 7), py = ty0 + (blk / kBlocksX) * 4 + (lane >> 3);
-            if (px < (int)a.width && py < (int)a.height) {
-                if (DEPTH_ONLY) a.depth[(size_t)py * a.width + px] = kFloatMin;
-                else a.keys[(size_t)py * a.width + px] = make_key(kFloatMin, kNoTri);
-            }
-        }
-        return;
-    }
-
-    unsigned long long best[kBlocksPerWarp];
-    float bestz[kBlocksPerWarp];
-#pragma unroll
-    for (int b = 0; b < kBlocksPerWarp; ++b) {
-        int blk = warp * kBlocksPerWarp + b;
-        int px = tx0 + (blk % kBlocksX) * 8 + (lane & 7), py = ty0 + (blk / kBlocksX) * 4 + (lane >> 3);
-        bool in = px < (int)a.width && py < (int)a.height;
-        if (DEPTH_ONLY) bestz[b] = (a.fresh || !in) ? kFloatMin : a.depth[(size_t)py * a.width + px];
-        else best[b] = (a.fresh || !in) ? make_key(kFloatMin, kNoTri) : a.keys[(size_t)py * a.width + px];
-    }
+    const uint32_t tile = blockIdx.y * a.tiles_x + blockIdx.x;
+    const uint32_t cell = (uint32_t)(ty0 / kCellH) * a.bins.cells_x + (uint32_t)(tx0 / kCellW);
+    const uint32_t n_bin = a.bins.count[a.bins.parity * a.bins.n_cells + cell];
+    const bool cleared = a.fresh || (!DEPTH_ONLY && a.tile_state[tile] != 0u);
+    // With a cleared frame the tile's RGB is rebuilt completely (zeros where nothing is drawn) and stored in bulk.
+    const bool rgb_bulk = SHADE && sa.fresh;
+    const int row_bytes = (tx1 - tx0 + 1) * 3;
 
     const bool use_bin = n_bin <= (uint32_t)kBinCap;
+    const uint32_t n_src = use_bin ? n_bin : a.n_triangles;
+    bool from_memory = !cleared;                          // later rounds of a long list merge with the earlier ones
+    bool touched = false;
     uint32_t scan_from = 0;
-    bool more = true;
+    bool more = n_src > 0;
     while (more) {
-        int n_list;
-        if (use_bin) {
-            // ---- (1a) the bin holds the tile's polygons ----
-            for (int i = tid; i < (int)n_bin; i += kRasterThreads) {
-                uint32_t t = a.bins.list[(size_t)tile * kBinCap + i];
-                stage_polygon(a, t, __ldg(&a.bbox[t]), i, tx0, ty0, tx1, ty1, s_tri, s_lo, s_hi);
+        // ---- (1) filter the source list (cell bin, or all polygons) against the tile, kListCap polygons per round ----
+        if (tid == 0) { s_count = 0; s_next = (int)n_src; s_block = 0; }
+        __syncthreads();
+        for (uint32_t base = scan_from; base < n_src; base += kRasterThreads) {
+            uint32_t i = base + tid, t = 0;
+            bool hit = false;
+            int4 bb = make_int4(1, 0, 0, 0);
+            if (i < n_src) {
+                t = use_bin ? a.bins.list[(size_t)cell * kBinCap + i] : i;
+                bb = __ldg(&a.bbox[t]);
+                hit = bb.x <= bb.z && bb.x <= tx1 && bb.z >= tx0 && bb.y <= ty1 && bb.w >= ty0;
             }
-            n_list = (int)n_bin;
-            more = false;
+            unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (lane == 0) s_warp_count[warp] = __popc(m);
             __syncthreads();
-        } else {
-            // ---- (1b) overflowed bin: scan all bounding boxes, kListCap polygons per round ----
-            if (tid == 0) { s_count = 0; s_next = (int)a.n_triangles; }
+            int before = s_count, total = 0;
+            for (int w = 0; w < kRasterThreads / 32; ++w) { int c = s_warp_count[w]; if (w < warp) before += c; total += c; }
+            int slot = before + __popc(m & ((1u << lane) - 1u));
+            bool overflow = s_count + total > kListCap;
+            if (hit && slot < kListCap) stage_polygon(a, t, bb, slot, tx0, ty0, tx1, ty1, s_tri, s_lo, s_hi);
+            if (hit && slot >= kListCap) atomicMin(&s_next, (int)i);       // first source entry that did not fit
             __syncthreads();
-            for (uint32_t base = scan_from; base < a.n_triangles; base += kRasterThreads) {
-                uint32_t t = base + tid;
-                bool hit = false;
-                int4 bb = make_int4(1, 0, 0, 0);
-                if (t < a.n_triangles) {
-                    bb = __ldg(&a.bbox[t]);
-                    hit = bb.x <= bb.z && bb.x <= tx1 && bb.z >= tx0 && bb.y <= ty1 && bb.w >= ty0;
-                }
-                unsigned m = __ballot_sync(0xffffffffu, hit);
-                if (lane == 0) s_warp_count[warp] = __popc(m);
-                __syncthreads();
-                int before = s_count, total = 0;
-                for (int w = 0; w < kRasterThreads / 32; ++w) { int c = s_warp_count[w]; if (w < warp) before += c; total += c; }
-                int slot = before + __popc(m & ((1u << lane) - 1u));
-                bool overflow = s_count + total > kListCap;
-                if (hit && slot < kListCap) stage_polygon(a, t, bb, slot, tx0, ty0, tx1, ty1, s_tri, s_lo, s_hi);
-                if (hit && slot >= kListCap) atomicMin(&s_next, (int)t);   // first polygon that did not fit
-                __syncthreads();
-                if (tid == 0) s_count = min(s_count + total, kListCap);
-                __syncthreads();
-                if (overflow) break;
-            }
-            n_list = s_count;
-            scan_from = (uint32_t)s_next;   // == n_triangles when everything was staged
-            more = scan_from < a.n_triangles;
+            if (tid == 0) s_count = min(s_count + total, kListCap);
+            __syncthreads();
+            if (overflow) break;
         }
+        const int n_list = s_count;
+        scan_from = (uint32_t)s_next;       // == n_src when everything was staged
+        more = scan_from < n_src;
+        if (n_list == 0) break;             // (more is false here: a round that staged nothing reached the end)
+        touched = true;
 
-        // ---- (2) per-warp blocks: ballot the staged bboxes against the block, evaluate per pixel ----
-#pragma unroll
-        for (int b = 0; b < kBlocksPerWarp; ++b) {
-            int blk = warp * kBlocksPerWarp + b;
-            int bx0 = (blk % kBlocksX) * 8, by0 = (blk / kBlocksX) * 4;   // tile-relative
-            int lx = bx0 + (lane & 7), ly = by0 + (lane >> 3);
+        // ---- (2) warps pull 8x4 blocks off the tile; ballot the staged bboxes against the block, evaluate per pixel ----
+        for (;;) {
+            int blk = 0;
+            if (lane == 0) blk = atomicAdd(&s_block, 1);
+            blk = __shfl_sync(0xffffffffu, blk, 0);
+            if (blk >= kBlocks) break;
+            const int bx0 = (blk % kBlocksX) * 8, by0 = (blk / kBlocksX) * 4;   // tile-relative
+            const int lx = bx0 + (lane & 7), ly = by0 + (lane >> 3);
+            const int px = tx0 + lx, py = ty0 + ly;
+            const bool in = px < (int)a.width && py < (int)a.height;
+            // running winner: depth, low key word (epoch | polygon; kNoTri = nothing drawn yet) and its barycentrics
+            float bz = kFloatMin, w0 = 0.0f, w1 = 0.0f, w2 = 0.0f;
+            uint32_t blo = kNoTri;
+            if (from_memory && in) {
+                if (DEPTH_ONLY) bz = a.depth[(size_t)py * a.width + px];
+                else { unsigned long long k = a.keys[(size_t)py * a.width + px]; bz = key_depth(k); blo = key_lo(k); }
+            }
+            bool fresh_winner = false;      // the winner was found in this round (its barycentrics are in w0..w2)
             for (int base = 0; base < n_list; base += 32) {
                 int i = base + lane;
                 bool cand = false;
@@ -207,7 +176,7 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a) {
                     m &= m - 1;
                     const int4* d = reinterpret_cast<const int4*>(s_tri + j * kStageWords);
                     int4 e = d[0], f = d[1];
-                    float z;
+                    float z, b0, b1, b2;
                     if (!((uint32_t)f.w & kInexactFlag)) {
                         int e1 = e.x + lx * e.y + ly * e.z;          // cx * sign(cz)
                         int e2 = e.w + lx * f.x + ly * f.y;          // cy * sign(cz)
@@ -215,35 +184,90 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a) {
                         if ((e0 | e1 | e2) < 0) continue;
                         int4 g = d[2];
                         float cx = (float)e1, cy = (float)e2, cz = (float)f.z;
-                        float b0 = 1.0f - (cx + cy) / cz, b1 = cx / cz, b2 = cy / cz;
+                        b0 = 1.0f - (cx + cy) / cz; b1 = cx / cz; b2 = cy / cz;
                         z = (b0 * __int_as_float(g.x) + b1 * __int_as_float(g.y)) + b2 * __int_as_float(g.z);
                     } else {
                         int4 g = d[2];
-                        float b0, b1, b2;
                         if (!fragment_depth(e.x, e.y, e.z, e.w, f.x, f.y, __int_as_float(g.x), __int_as_float(g.y), __int_as_float(g.z),
-                                            tx0 + lx, ty0 + ly, z, b0, b1, b2)) continue;
+                                            px, py, z, b0, b1, b2)) continue;
                     }
                     if (z != z) { atomicAdd(&a.diag[D_NAN_DEPTH], 1ull); continue; }
                     if (DEPTH_ONLY) {
-                        if (z >= bestz[b]) bestz[b] = z;                         // shader.rs:703
+                        if (z >= bz) bz = z;                                     // shader.rs:703
                     } else {
-                        unsigned long long k = make_key(z, (a.epoch << 24) | ((uint32_t)f.w & kTriMask));
-                        if (key_beats(k, best[b])) best[b] = k;                  // shader.rs:175
+                        // shader.rs:175 `z <= zbuf -> reject`, applied in polygon order == key_beats() on packed keys
+                        uint32_t lo = (a.epoch << 24) | ((uint32_t)f.w & kTriMask);
+                        if (z > bz || (z == bz && lo < blo && blo != kNoTri)) {
+                            bz = z; blo = lo;
+                            if (SHADE) { w0 = b0; w1 = b1; w2 = b2; fresh_winner = true; }
+                        }
                     }
                 }
             }
+            if (in) {
+                if (DEPTH_ONLY) a.depth[(size_t)py * a.width + px] = bz;
+                else a.keys[(size_t)py * a.width + px] = make_key(bz, blo);
+            }
+            if (SHADE && !more) {
+                // ---- (3) fragment stage for the winner, if it passed the depth test in THIS render ----
+                uint32_t out = 0u;
+                const bool shaded = in && blo != kNoTri && (blo >> 24) == a.epoch;
+                if (shaded) {
+                    if (!fresh_winner) {        // won in an earlier round of a long list: re-derive its barycentrics
+                        const float4* r = a.rec + (size_t)(blo & kTriMask) * 4;
+                        float4 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
+                        float zz;
+                        fragment_depth(__float_as_int(r0.x), __float_as_int(r0.y), __float_as_int(r0.z), __float_as_int(r0.w),
+                                       __float_as_int(r1.x), __float_as_int(r1.y), r1.z, r1.w, r2.x, px, py, zz, w0, w1, w2);
+                    }
+                    out = shade_pixel<SHADE ? MODE : 0>(sa, u, blo & kTriMask, px, py, bz, w0, w1, w2);
+                }
+                if (rgb_bulk) {
+                    uint8_t* p = s_rgb + ly * kRgbRow + lx * 3;
+                    p[0] = (uint8_t)out; p[1] = (uint8_t)(out >> 8); p[2] = (uint8_t)(out >> 16);
+                } else if (shaded) {
+                    uint8_t* p = sa.rgb + ((size_t)(a.height - 1 - py) * a.width + px) * 3;
+                    p[0] = (uint8_t)out; p[1] = (uint8_t)(out >> 8); p[2] = (uint8_t)(out >> 16);
+                }
+            }
         }
+        from_memory = true;
         __syncthreads();
     }
 
-    // ---- (3) write the tile once ----
-#pragma unroll
-    for (int b = 0; b < kBlocksPerWarp; ++b) {
-        int blk = warp * kBlocksPerWarp + b;
-        int px = tx0 + (blk % kBlocksX) * 8 + (lane & 7), py = ty0 + (blk / kBlocksX) * 4 + (lane >> 3);
-        if (px < (int)a.width && py < (int)a.height) {
-            if (DEPTH_ONLY) a.depth[(size_t)py * a.width + px] = bestz[b];
-            else a.keys[(size_t)py * a.width + px] = best[b];
+    if (!touched) {
+        // Nothing touches this tile: an uncleared target keeps its contents, a cleared one its cleared state.
+        if (cleared) {
+            if (DEPTH_ONLY) {
+                for (int i = tid; i < kTileW * kTileH; i += kRasterThreads) {
+                    int px = tx0 + i % kTileW, py = ty0 + i / kTileW;
+                    if (px < (int)a.width && py < (int)a.height) a.depth[(size_t)py * a.width + px] = kFloatMin;
+                }
+            } else if (tid == 0) {
+                a.tile_state[tile] = 1u;
+            }
+        }
+    } else if (!DEPTH_ONLY && tid == 0) {
+        a.tile_state[tile] = 0u;
+    }
+
+    if (rgb_bulk) {
+        // ---- (4) the tile's RGB, top-down rows, 16-byte stores when the frame layout allows ----
+        const int rows = ty1 - ty0 + 1;
+        if ((a.width & 15u) == 0u) {
+            const int vec_per_row = row_bytes >> 4;             // tile widths are multiples of 16 px here
+            for (int i = tid; i < rows * vec_per_row; i += kRasterThreads) {
+                int r = i / vec_per_row, c = i % vec_per_row;
+                uint4 v = touched ? *reinterpret_cast<const uint4*>(s_rgb + r * kRgbRow + c * 16) : make_uint4(0u, 0u, 0u, 0u);
+                uint8_t* dst = sa.rgb + ((size_t)(a.height - 1 - (ty0 + r)) * a.width + tx0) * 3;
+                reinterpret_cast<uint4*>(dst)[c] = v;
+            }
+        } else {
+            for (int i = tid; i < rows * row_bytes; i += kRasterThreads) {
+                int r = i / row_bytes, c = i % row_bytes;
+                uint8_t* dst = sa.rgb + ((size_t)(a.height - 1 - (ty0 + r)) * a.width + tx0) * 3;
+                dst[c] = touched ? s_rgb[r * kRgbRow + c] : (uint8_t)0;
+            }
         }
     }
 }

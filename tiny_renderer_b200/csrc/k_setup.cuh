@@ -3,8 +3,7 @@
 // (/root/reference/src/scene/shader.rs:285-316, 349-384, 416-437, 475-496, 549-595, 671-692, 711-747,
 // 809-830, 849-870), their helpers (shader.rs:116-165) and the bounding box of scene.rs:232-239.
 #pragma once
-#include "tr_types.cuh"
-#include "k_raster.cuh"
+#include "k_tile.cuh"
 
 namespace tr {
 
@@ -16,7 +15,7 @@ struct SetupOut {
     float4* rec;      // n_triangles x 4 float4 (kRecWords)
     float4* var;      // n_triangles x 6 float4 (kVarWords), may be null when the pipeline needs none
     int4* bbox;       // n_triangles: xmin ymin xmax ymax clamped to the screen; xmin > xmax when not drawn
-    Bins bins;        // K2: per-tile polygon lists for the raster kernel that follows
+    Bins bins;        // K2: per-cell polygon lists for the raster kernel that follows
 };
 
 // it_m * (n, 0) -> must have w == 0 -> normalised   (shader.rs:300-303, 368-371)
@@ -65,28 +64,32 @@ __global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__
     int32_t ymin = max(0, min(min(ry[0], ry[1]), ry[2])), ymax = min(max(max(ry[0], ry[1]), ry[2]), (int32_t)u.height - 1);
     if (!drawn || ymin > ymax) { xmin = 1; xmax = 0; }
     if (valid) out.bbox[t] = make_int4(xmin, ymin, xmax, ymax);
-    // K2 bin (fused): append the polygon to every screen tile its clamped bounding box touches.  The order inside
-    // a bin is whatever the atomics give; visibility does not depend on it (packed-key min is commutative).
-    // The warp walks its 32 polygons one after the other with the lanes spread over the polygon's tiles, so a
-    // polygon covering dozens of tiles costs one round of independent atomics instead of a serial chain.
+    // K2 bin (fused): append the polygon to every binning cell its clamped bounding box touches.  The order inside
+    // a bin is whatever the atomics give; visibility does not depend on it (the packed-key min is commutative).
+    // All appends of a thread are issued back to back (independent atomics, one round trip); only polygons that
+    // cover more than kSmallCells cells are walked by the whole warp, lanes spread over the polygon's cells.
     {
+        // zero the counter set the NEXT pass will fill (its last reader finished before this kernel started)
+        uint32_t* other = out.bins.count + (out.bins.parity ^ 1u) * out.bins.n_cells;
+        for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < out.bins.n_cells; c += gridDim.x * blockDim.x) other[c] = 0u;
+        uint32_t* count = out.bins.count + out.bins.parity * out.bins.n_cells;
+        constexpr int kSmallCells = 6;
         const bool any = valid && xmin <= xmax;
-        const int bx0 = any ? xmin / kTileW : 0, by0 = any ? ymin / kTileH : 0;
-        const int nx = any ? xmax / kTileW - bx0 + 1 : 0, ny = any ? ymax / kTileH - by0 + 1 : 0;
+        const int bx0 = any ? xmin / kCellW : 0, by0 = any ? ymin / kCellH : 0;
+        const int nx = any ? xmax / kCellW - bx0 + 1 : 0, ny = any ? ymax / kCellH - by0 + 1 : 0;
         const int lane = threadIdx.x & 31;
         const unsigned peers = 0xffffffffu;
-        // Small footprints (<= 4 tiles, the common case): the owning thread issues its atomics back to back.
-        const bool small = any && nx * ny <= 4;
+        const bool small = any && nx * ny <= kSmallCells;
         if (small) {
-            uint32_t tl[4], sl[4];
+            uint32_t tl[kSmallCells], sl[kSmallCells];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                tl[i] = (uint32_t)(by0 + i / nx) * out.bins.tiles_x + (uint32_t)(bx0 + i % nx);
+            for (int i = 0; i < kSmallCells; ++i) {
+                tl[i] = (uint32_t)(by0 + i / nx) * out.bins.cells_x + (uint32_t)(bx0 + i % nx);
                 sl[i] = kBinCap;
-                if (i < nx * ny) sl[i] = atomicAdd(&out.bins.count[tl[i]], 1u);
+                if (i < nx * ny) sl[i] = atomicAdd(&count[tl[i]], 1u);
             }
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < kSmallCells; ++i)
                 if (sl[i] < (uint32_t)kBinCap) out.bins.list[(size_t)tl[i] * kBinCap + sl[i]] = t;
         }
         unsigned todo = __ballot_sync(peers, any && !small);
@@ -97,9 +100,9 @@ __global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__
             const int snx = __shfl_sync(peers, nx, src), sny = __shfl_sync(peers, ny, src);
             const uint32_t st = __shfl_sync(peers, t, src);
             for (int i = lane; i < snx * sny; i += 32) {
-                uint32_t tile = (uint32_t)(sby0 + i / snx) * out.bins.tiles_x + (uint32_t)(sbx0 + i % snx);
-                uint32_t slot = atomicAdd(&out.bins.count[tile], 1u);
-                if (slot < (uint32_t)kBinCap) out.bins.list[(size_t)tile * kBinCap + slot] = st;
+                uint32_t cell = (uint32_t)(sby0 + i / snx) * out.bins.cells_x + (uint32_t)(sbx0 + i % snx);
+                uint32_t slot = atomicAdd(&count[cell], 1u);
+                if (slot < (uint32_t)kBinCap) out.bins.list[(size_t)cell * kBinCap + slot] = st;
             }
         }
     }

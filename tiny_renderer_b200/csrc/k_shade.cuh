@@ -1,14 +1,13 @@
-// k_shade.cuh — K5 deferred shading (seven pipelines) and K6 ambient-occlusion accumulation.
+// k_shade.cuh — K5 fragment stage of the seven pipelines (device functions, called from the fused tile kernel in
+// k_raster.cuh for the winner of every pixel) and K6 ambient-occlusion accumulation (deferred, many-light batch).
 //
-// One thread shades four horizontally adjacent pixels: it reads their visibility keys, re-derives the
-// barycentric coordinates of the winning polygon with the reference's arithmetic, runs the pipeline's
-// fragment math and writes 12 contiguous bytes of top-down RGB8.  Texels are point-sampled through texture
-// objects (the texture path).  Replaces the fragment closures of /root/reference/src/scene/shader.rs
-// (:318-333 default, :386-401 phong, :439-459 normal_map, :498-534 specular, :597-655 darboux, :749-788 shadow,
-// :872-947 occlusion), the samplers of /root/reference/src/scene/util.rs:34-83 and color_blend (util.rs:7-13).
+// Texels are point-sampled through texture objects (the texture path).  Replaces the fragment closures of
+// /root/reference/src/scene/shader.rs (:318-333 default, :386-401 phong, :439-459 normal_map, :498-534 specular,
+// :597-655 darboux, :749-788 shadow, :872-947 occlusion), the samplers of /root/reference/src/scene/util.rs:34-83
+// and color_blend (util.rs:7-13).
 #pragma once
 #include <cuda_runtime.h>
-#include "k_raster.cuh"
+#include "k_tile.cuh"
 
 namespace tr {
 
@@ -19,6 +18,8 @@ struct Maps {
 
 struct ShadeArgs {
     const unsigned long long* keys;
+    const uint32_t* tile_state;     // per raster tile: 1 = cleared, keys of the tile are stale (k_raster.cuh)
+    uint32_t tiles_x;
     const float4* rec;
     const float4* var;
     const float* shadow;
@@ -55,14 +56,13 @@ __device__ __forceinline__ float shadow_lookup(const float* shadow, f3 s, uint32
     return __ldg(&shadow[idx]);
 }
 
-// Fragment math of one pipeline for one covered pixel; returns packed RGB.
+// Fragment math of one pipeline for one covered pixel; returns packed RGB.  z and (b0, b1, b2) are the depth and the
+// barycentric coordinates of the pixel in polygon `tri` as the reference computes them (scene.rs:178-196).
 template <int PIPE>
-__device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Uniforms& u, uint32_t tri, int px, int py) {
+__device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Uniforms& u, uint32_t tri, int px, int py,
+                                                float z, float b0, float b1, float b2) {
     const float4* r = a.rec + (size_t)tri * 4;
-    float4 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2), r3 = __ldg(r + 3);
-    float z, b0, b1, b2;
-    fragment_depth(__float_as_int(r0.x), __float_as_int(r0.y), __float_as_int(r0.z), __float_as_int(r0.w),
-                   __float_as_int(r1.x), __float_as_int(r1.y), r1.z, r1.w, r2.x, px, py, z, b0, b1, b2);
+    float4 r2 = __ldg(r + 2), r3 = __ldg(r + 3);
     // uv = vertex_uvs * bar (2x3 mat-vec, column order)
     f2 uv{(r2.z * b0 + r2.w * b1) + r3.x * b2, (r3.y * b0 + r3.z * b1) + r3.w * b2};
     const float4* v = a.var + (size_t)tri * 6;
@@ -146,46 +146,27 @@ __device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Unifor
     return pack_rgb(blend_black(c.x, diff), blend_black(c.y, diff), blend_black(c.z, diff));
 }
 
-// ACCUM: K6 — add the occlusion gray of every covered pixel into ao_accum instead of writing RGB.
-template <int PIPE, bool ACCUM>
-__global__ void __launch_bounds__(256) k_shade(const ShadeArgs a, const Uniforms u) {
-    const uint32_t groups_per_row = (u.width + 3) / 4;
-    uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= groups_per_row * u.height) return;
-    const int py = (int)(gid / groups_per_row), px0 = (int)(gid % groups_per_row) * 4;
-    uint32_t out[4];
-    bool shaded[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        int px = px0 + k;
-        out[k] = 0u; shaded[k] = false;
-        if (px >= (int)u.width) continue;
-        unsigned long long key = __ldg(&a.keys[(size_t)py * u.width + px]);
-        uint32_t lo = key_lo(key);
-        // Only fragments that passed the depth test in THIS render are shaded (earlier renders keep their colour).
-        if (lo == kNoTri || (lo >> 24) != (ACCUM ? 0u : u.epoch)) continue;
-        out[k] = shade_pixel<PIPE>(a, u, lo & kTriMask, px, py);
-        shaded[k] = true;
-    }
-    if (ACCUM) {
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            if (shaded[k]) a.ao_accum[(size_t)py * u.width + px0 + k] += out[k] & 0xffu;
-        return;
-    }
-    uint8_t* row = a.rgb + (size_t)(u.height - 1 - py) * u.width * 3;
-    if (a.fresh && (u.width & 3u) == 0u) {
-        uint32_t w0 = out[0] | (out[1] << 24), w1 = (out[1] >> 8) | (out[2] << 16), w2 = (out[2] >> 16) | (out[3] << 8);
-        uint32_t* dst = reinterpret_cast<uint32_t*>(row + (size_t)px0 * 3);
-        dst[0] = w0; dst[1] = w1; dst[2] = w2;
-    } else {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            int px = px0 + k;
-            if (px >= (int)u.width || !(shaded[k] || a.fresh)) continue;
-            row[px * 3 + 0] = (uint8_t)(out[k]); row[px * 3 + 1] = (uint8_t)(out[k] >> 8); row[px * 3 + 2] = (uint8_t)(out[k] >> 16);
-        }
-    }
+// K6 ao_accumulate — deferred occlusion pass of the many-light AO batch: adds the occlusion gray of every covered
+// pixel into ao_accum (u32, bottom-up).  One thread per pixel; a warp covers 32 consecutive pixels of one row (rows
+// are padded to a multiple of 32 threads), which always lie inside one raster tile.
+constexpr int kShadeThreads = 256;
+__host__ __device__ inline uint32_t shade_threads_per_row(uint32_t width) { return (width + 31u) & ~31u; }
+
+__global__ void __launch_bounds__(kShadeThreads) k_ao_accumulate(const ShadeArgs a, const Uniforms u) {
+    const uint32_t tpr = shade_threads_per_row(u.width);
+    const size_t gid = (size_t)blockIdx.x * kShadeThreads + threadIdx.x;
+    const int py = (int)(gid / tpr), px = (int)(gid % tpr);
+    if (py >= (int)u.height || px >= (int)u.width) return;
+    // A cleared tile has no winners and its keys are stale.
+    if (a.tile_state[(uint32_t)(py / kTileH) * a.tiles_x + (uint32_t)(px / kTileW)] != 0u) return;
+    const uint32_t lo = key_lo(__ldg(&a.keys[(size_t)py * u.width + px]));
+    if (lo == kNoTri || (lo >> 24) != 0u) return;
+    const float4* r = a.rec + (size_t)(lo & kTriMask) * 4;
+    float4 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
+    float z, b0, b1, b2;
+    fragment_depth(__float_as_int(r0.x), __float_as_int(r0.y), __float_as_int(r0.z), __float_as_int(r0.w),
+                   __float_as_int(r1.x), __float_as_int(r1.y), r1.z, r1.w, r2.x, px, py, z, b0, b1, b2);
+    a.ao_accum[(size_t)py * u.width + px] += shade_pixel<P_OCCLUSION>(a, u, lo & kTriMask, px, py, z, b0, b1, b2) & 0xffu;
 }
 
 }  // namespace tr

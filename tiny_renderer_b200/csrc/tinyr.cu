@@ -41,11 +41,12 @@ struct tr_scene {
     float4* geom = nullptr;
     SetupOut cam{}, lit{};
     std::vector<unsigned long long*> keys;
+    std::vector<uint32_t*> tile_state;   // per keys buffer, per raster tile: 1 = cleared, key memory stale
     std::vector<uint8_t*> rgb;
     float* shadow = nullptr;
     uint32_t* ao = nullptr;
     unsigned long long* diag = nullptr;
-    Bins bins{};
+    struct { Bins b{}; uint32_t tiles_x = 0, tiles_y = 0; } bins;
     unsigned long long* d_checksums = nullptr; size_t checksum_cap = 0;
     uint8_t* scratch = nullptr; size_t scratch_bytes = 0;
     cudaArray_t arrays[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -111,12 +112,19 @@ int fill_state(tr_scene* s, float z_init, bool do_keys, bool do_shadow, bool do_
     Scoped sp(s, KS_CLEAR);
     k_fill_state<<<148 * 8, 256, 0, s->stream>>>(s->keys[s->cur], s->shadow, reinterpret_cast<uint32_t*>(s->rgb[s->cur]), s->n_px,
                                                  (s->n_px * 3 + 3) / 4, z_init, do_keys, do_shadow, do_rgb);
+    if (do_keys) CU(cudaMemsetAsync(s->tile_state[s->cur], 0, (size_t)s->bins.tiles_x * s->bins.tiles_y * 4, s->stream));
     return launch_ok("k_fill_state");
 }
 
 // Turn pending (lazy) clears into memory contents, for getters that read state a render has not rewritten.
 int materialise(tr_scene* s) {
     int rc = fill_state(s, -3.402823466e38f, s->fresh_keys, s->fresh_shadow, s->fresh_rgb);
+    if (rc == TR_OK && !s->fresh_keys) {
+        // tiles still in the tile-level cleared state: write their keys out
+        Scoped sp(s, KS_CLEAR);
+        k_materialise_tiles<<<dim3(s->bins.tiles_x, s->bins.tiles_y), 256, 0, s->stream>>>(s->keys[s->cur], s->tile_state[s->cur], s->width, s->height);
+        rc = launch_ok("k_materialise_tiles");
+    }
     s->fresh_keys = s->fresh_shadow = s->fresh_rgb = false;
     return rc;
 }
@@ -212,13 +220,17 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
     s->bins.tiles_x = (s->width + kTileW - 1) / kTileW;
     s->bins.tiles_y = (s->height + kTileH - 1) / kTileH;
     const size_t n_tiles = (size_t)s->bins.tiles_x * s->bins.tiles_y;
-    CU(cudaMalloc(&s->bins.count, n_tiles * 4));
-    CU(cudaMemset(s->bins.count, 0, n_tiles * 4));
-    CU(cudaMalloc(&s->bins.list, n_tiles * kBinCap * 4));
-    s->cam.bins = s->bins;
-    s->lit.bins = s->bins;
-    s->keys.assign(s->ring, nullptr); s->rgb.assign(s->ring, nullptr);
+    s->bins.b.cells_x = (s->width + kCellW - 1) / kCellW;
+    s->bins.b.cells_y = (s->height + kCellH - 1) / kCellH;
+    s->bins.b.n_cells = s->bins.b.cells_x * s->bins.b.cells_y;
+    s->bins.b.parity = 0;
+    CU(cudaMalloc(&s->bins.b.count, (size_t)s->bins.b.n_cells * 2 * 4));
+    CU(cudaMemset(s->bins.b.count, 0, (size_t)s->bins.b.n_cells * 2 * 4));
+    CU(cudaMalloc(&s->bins.b.list, (size_t)s->bins.b.n_cells * kBinCap * 4));
+    s->keys.assign(s->ring, nullptr); s->rgb.assign(s->ring, nullptr); s->tile_state.assign(s->ring, nullptr);
     for (uint32_t r = 0; r < s->ring; ++r) {
+        CU(cudaMalloc(&s->tile_state[r], n_tiles * 4));
+        CU(cudaMemset(s->tile_state[r], 0, n_tiles * 4));
         CU(cudaMalloc(&s->keys[r], s->n_px * 8));
         CU(cudaMalloc(&s->rgb[r], s->n_px * 3 + 16));
     }
@@ -249,10 +261,11 @@ void destroy_impl(tr_scene* s) {
         if (s->arrays[k]) cudaFreeArray(s->arrays[k]);
     }
     for (auto p : s->keys) cudaFree(p);
+    for (auto p : s->tile_state) cudaFree(p);
     for (auto p : s->rgb) cudaFree(p);
     cudaFree(s->geom); cudaFree(s->cam.rec); cudaFree(s->cam.var); cudaFree(s->cam.bbox);
     cudaFree(s->lit.rec); cudaFree(s->lit.bbox);
-    cudaFree(s->bins.count); cudaFree(s->bins.list);
+    cudaFree(s->bins.b.count); cudaFree(s->bins.b.list);
     cudaFree(s->shadow); cudaFree(s->ao); cudaFree(s->diag); cudaFree(s->d_checksums); cudaFree(s->scratch);
     if (s->own_stream) cudaStreamDestroy(s->own_stream);
     delete s;
@@ -264,45 +277,60 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     if (s->n_tri == 0) return TR_OK;
     Scoped sp(s, KS_SETUP);
     dim3 grid((s->n_tri + 127) / 128);
+    s->bins.b.parity ^= 1u;                 // this pass fills the other counter set; the kernel zeroes the one just used
+    s->cam.bins = s->bins.b;
+    s->lit.bins = s->bins.b;
     if (light_pass) k_vertex_setup<true><<<grid, 128, 0, s->stream>>>(s->geom, s->lit, u, s->pipeline, s->diag);
     else k_vertex_setup<false><<<grid, 128, 0, s->stream>>>(s->geom, s->cam, u, s->pipeline, s->diag);
     return launch_ok("k_vertex_setup");
 }
 
-int run_raster(tr_scene* s, bool depth_only, uint32_t epoch, bool fresh) {
+ShadeArgs shade_args(tr_scene* s, bool fresh_rgb) {
+    ShadeArgs a{};
+    a.keys = s->keys[s->cur]; a.tile_state = s->tile_state[s->cur]; a.tiles_x = s->bins.tiles_x;
+    a.rec = s->cam.rec; a.var = s->cam.var; a.shadow = s->shadow;
+    a.rgb = s->rgb[s->cur]; a.ao_accum = s->ao; a.diag = s->diag; a.maps = s->maps; a.fresh = fresh_rgb ? 1 : 0;
+    return a;
+}
+
+// mode: kModeDepthOnly (K4), kModeVisibility (K3 alone) or a pipeline id (K3 + K5 fused).
+int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms& u, bool fresh_rgb) {
+    const bool depth_only = mode == kModeDepthOnly;
     RasterArgs a{};
     a.rec = depth_only ? s->lit.rec : s->cam.rec;
     a.bbox = depth_only ? s->lit.bbox : s->cam.bbox;
-    a.bins = s->bins;
-    a.n_triangles = s->n_tri; a.width = s->width; a.height = s->height;
+    a.bins = s->bins.b;
+    a.n_triangles = s->n_tri; a.width = s->width; a.height = s->height; a.tiles_x = s->bins.tiles_x;
     a.epoch = epoch; a.fresh = fresh ? 1 : 0;
-    a.keys = s->keys[s->cur]; a.depth = s->shadow; a.diag = s->diag;
-    dim3 grid((s->width + kTileW - 1) / kTileW, (s->height + kTileH - 1) / kTileH);
+    a.keys = s->keys[s->cur]; a.tile_state = s->tile_state[s->cur]; a.depth = s->shadow; a.diag = s->diag;
+    ShadeArgs sa = shade_args(s, fresh_rgb);
+    dim3 grid(s->bins.tiles_x, s->bins.tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
-    if (depth_only) k_raster<true><<<grid, kRasterThreads, 0, s->stream>>>(a);
-    else k_raster<false><<<grid, kRasterThreads, 0, s->stream>>>(a);
+#define TR_RASTER(M) k_raster<M><<<grid, kRasterThreads, 0, s->stream>>>(a, sa, u)
+    switch (mode) {
+        case kModeDepthOnly: TR_RASTER(kModeDepthOnly); break;
+        case kModeVisibility: TR_RASTER(kModeVisibility); break;
+        case P_DEFAULT: TR_RASTER(P_DEFAULT); break;
+        case P_PHONG: TR_RASTER(P_PHONG); break;
+        case P_NORMAL_MAP: TR_RASTER(P_NORMAL_MAP); break;
+        case P_SPECULAR: TR_RASTER(P_SPECULAR); break;
+        case P_DARBOUX: TR_RASTER(P_DARBOUX); break;
+        case P_SHADOW: TR_RASTER(P_SHADOW); break;
+        default: TR_RASTER(P_OCCLUSION); break;
+    }
+#undef TR_RASTER
+    if (!depth_only && mode != kModeVisibility) s->kernel_launches[KS_SHADE]++;     // K5 runs inside this launch
     return launch_ok("k_raster");
 }
 
-template <bool ACCUM>
-int run_shade(tr_scene* s, const Uniforms& u, bool fresh_rgb) {
-    ShadeArgs a{};
-    a.keys = s->keys[s->cur]; a.rec = s->cam.rec; a.var = s->cam.var; a.shadow = s->shadow;
-    a.rgb = s->rgb[s->cur]; a.ao_accum = s->ao; a.diag = s->diag; a.maps = s->maps; a.fresh = fresh_rgb ? 1 : 0;
-    size_t groups = (size_t)((s->width + 3) / 4) * s->height;
-    dim3 grid((unsigned)((groups + 255) / 256));
-    Scoped sp(s, ACCUM ? KS_AO : KS_SHADE);
-    if (ACCUM) { k_shade<P_OCCLUSION, true><<<grid, 256, 0, s->stream>>>(a, u); return launch_ok("k_shade<occlusion,accum>"); }
-    switch (s->pipeline) {
-        case P_DEFAULT: k_shade<P_DEFAULT, false><<<grid, 256, 0, s->stream>>>(a, u); break;
-        case P_PHONG: k_shade<P_PHONG, false><<<grid, 256, 0, s->stream>>>(a, u); break;
-        case P_NORMAL_MAP: k_shade<P_NORMAL_MAP, false><<<grid, 256, 0, s->stream>>>(a, u); break;
-        case P_SPECULAR: k_shade<P_SPECULAR, false><<<grid, 256, 0, s->stream>>>(a, u); break;
-        case P_DARBOUX: k_shade<P_DARBOUX, false><<<grid, 256, 0, s->stream>>>(a, u); break;
-        case P_SHADOW: k_shade<P_SHADOW, false><<<grid, 256, 0, s->stream>>>(a, u); break;
-        default: k_shade<P_OCCLUSION, false><<<grid, 256, 0, s->stream>>>(a, u); break;
-    }
-    return launch_ok("k_shade");
+// K6: deferred occlusion pass of the many-light AO batch.
+int run_ao_accumulate(tr_scene* s, const Uniforms& u) {
+    ShadeArgs a = shade_args(s, false);
+    size_t threads = (size_t)shade_threads_per_row(s->width) * s->height;
+    dim3 grid((unsigned)((threads + kShadeThreads - 1) / kShadeThreads));
+    Scoped sp(s, KS_AO);
+    k_ao_accumulate<<<grid, kShadeThreads, 0, s->stream>>>(a, u);
+    return launch_ok("k_ao_accumulate");
 }
 
 // Scene::render (scene.rs:151-268): every pass = prepare, all polygons through the vertex stage, raster.
@@ -316,16 +344,15 @@ int render_impl(tr_scene* s) {
         if ((rc = prep_error(prepare_light(u, s->width, s->height, s->light, s->at, s->up)))) return rc;
         u.n_triangles = s->n_tri; u.epoch = s->epoch;
         if ((rc = run_setup(s, u, true))) return rc;
-        if ((rc = run_raster(s, true, s->epoch, s->fresh_shadow))) return rc;
+        if ((rc = run_raster(s, kModeDepthOnly, s->epoch, s->fresh_shadow, u, false))) return rc;
         s->fresh_shadow = false;
         if ((rc = prep_error(prepare_camera_with_shadow(u, s->width, s->height, s->light, s->from, s->at, s->up, s->pipeline == P_OCCLUSION)))) return rc;
     } else {
         if ((rc = prep_error(prepare_camera(u, s->width, s->height, s->light, s->from, s->at, s->up)))) return rc;
     }
     if ((rc = run_setup(s, u, false))) return rc;
-    if ((rc = run_raster(s, false, s->epoch, s->fresh_keys))) return rc;
+    if ((rc = run_raster(s, s->pipeline, s->epoch, s->fresh_keys, u, s->fresh_rgb))) return rc;
     s->fresh_keys = false;
-    if ((rc = run_shade<false>(s, u, s->fresh_rgb))) return rc;
     s->fresh_rgb = false;
     s->uni = u;
     s->epoch++;
