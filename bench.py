@@ -242,13 +242,13 @@ def run_gpu(args, rank, world, local_rank):
     value = world * args.steps * frames_per_step * n_px / (ms * 1e-3) / 1e6
 
     # ---- e2e: the reference-facing calls with a HOST destination, D2H inside the timed region ----
-    host = tr.pinned_empty((H4K, W4K, 3), np.uint8)
+    # One pinned host buffer per frame of the step: tr_scene_render_views copies every finished frame to the host
+    # (asynchronously, on the frame's own stream, so copies overlap the next frames' rendering) and returns when
+    # all of them have landed.
+    host = tr.pinned_empty((len(PIPES), N_ANGLES, H4K, W4K, 3), np.uint8)
     def e2e_step():
-        for p in PIPES:
-            s = scenes[p]
-            for v in views:
-                s.clear(); s.set_light_direction(v[9:12]); s.set_camera(v[0:3], v[3:6], v[6:9]); s.render()
-                s.get_frame_buffer(out=host)
+        for i, p in enumerate(PIPES):
+            scenes[p].render_views(views, want_checksums=False, frames_out=host[i])
     e2e_step()
     barrier()
     t0 = time.perf_counter()
@@ -268,8 +268,9 @@ def run_gpu(args, rank, world, local_rank):
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": data, "config": workload_config(),
             "e2e": {"value": e2e_value, "unit": "Mpixels/s", "h2d_bytes_per_step": frames_per_step * 48,
                     "d2h_bytes_per_step": frames_per_step * n_px * 3,
-                    "note": "clear/set_light_direction/set_camera/render/get_frame_buffer per frame into pinned host memory; "
-                            "inputs are the 12 floats of camera+light per frame (kernel arguments)"},
+                    "note": "tr_scene_render_views(views, frames -> pinned host): per frame clear/set_light_direction/set_camera/"
+                            "render + device->host copy of the RGB8 frame, all inside the timed region; inputs are the 12 "
+                            "floats of camera+light per frame (kernel arguments); PCIe-bound: 24.9 MB per frame"},
             "gpu_launches": int(launches), "clocks": clocks}
 
     if rank == 0:

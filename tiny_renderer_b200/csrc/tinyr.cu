@@ -39,20 +39,29 @@ struct tr_scene {
     // device
     cudaStream_t own_stream = nullptr, stream = nullptr;
     float4* geom = nullptr;
-    SetupOut cam{}, lit{};
-    std::vector<unsigned long long*> keys;
-    std::vector<uint32_t*> tile_state;   // per keys buffer, per raster tile: 1 = cleared, key memory stale
-    std::vector<uint8_t*> rgb;
-    float* shadow = nullptr;
+    // One slot = everything a frame in flight owns, so that consecutive frames of a view batch can overlap on the
+    // GPU (tr_scene_render_views rotates through the slots, each on its own stream).  The single-frame API works on
+    // slot `cur` and the scene stream.
+    struct Slot {
+        unsigned long long* keys = nullptr;
+        uint32_t* tile_state = nullptr;    // per raster tile: 1 = cleared, key memory stale
+        uint8_t* rgb = nullptr;
+        float* shadow = nullptr;
+        SetupOut cam{}, lit{};
+        Bins bins{};
+        cudaStream_t stream = nullptr;
+        cudaEvent_t done = nullptr;
+    };
+    std::vector<Slot> slots;
+    uint32_t tiles_x = 0, tiles_y = 0;
     uint32_t* ao = nullptr;
     unsigned long long* diag = nullptr;
-    struct { Bins b{}; uint32_t tiles_x = 0, tiles_y = 0; } bins;
     unsigned long long* d_checksums = nullptr; size_t checksum_cap = 0;
     uint8_t* scratch = nullptr; size_t scratch_bytes = 0;
     cudaArray_t arrays[4] = {nullptr, nullptr, nullptr, nullptr};
     Maps maps{};
     // timing
-    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_fork = nullptr;
     bool profiling = false;
     struct Span { int slot; cudaEvent_t a, b; };
     std::vector<Span> spans;
@@ -62,6 +71,8 @@ struct tr_scene {
 };
 
 namespace {
+
+inline tr_scene::Slot& S(tr_scene* s) { return s->slots[s->cur]; }
 
 int pipeline_from_name(const char* name) {
     if (!name) return -1;
@@ -110,9 +121,9 @@ int launch_ok(const char* what) {
 int fill_state(tr_scene* s, float z_init, bool do_keys, bool do_shadow, bool do_rgb) {
     if (!do_keys && !do_shadow && !do_rgb) return TR_OK;
     Scoped sp(s, KS_CLEAR);
-    k_fill_state<<<148 * 8, 256, 0, s->stream>>>(s->keys[s->cur], s->shadow, reinterpret_cast<uint32_t*>(s->rgb[s->cur]), s->n_px,
+    k_fill_state<<<148 * 8, 256, 0, s->stream>>>(S(s).keys, S(s).shadow, reinterpret_cast<uint32_t*>(S(s).rgb), s->n_px,
                                                  (s->n_px * 3 + 3) / 4, z_init, do_keys, do_shadow, do_rgb);
-    if (do_keys) CU(cudaMemsetAsync(s->tile_state[s->cur], 0, (size_t)s->bins.tiles_x * s->bins.tiles_y * 4, s->stream));
+    if (do_keys) CU(cudaMemsetAsync(S(s).tile_state, 0, (size_t)s->tiles_x * s->tiles_y * 4, s->stream));
     return launch_ok("k_fill_state");
 }
 
@@ -122,7 +133,7 @@ int materialise(tr_scene* s) {
     if (rc == TR_OK && !s->fresh_keys) {
         // tiles still in the tile-level cleared state: write their keys out
         Scoped sp(s, KS_CLEAR);
-        k_materialise_tiles<<<dim3(s->bins.tiles_x, s->bins.tiles_y), 256, 0, s->stream>>>(s->keys[s->cur], s->tile_state[s->cur], s->width, s->height);
+        k_materialise_tiles<<<dim3(s->tiles_x, s->tiles_y), 256, 0, s->stream>>>(S(s).keys, S(s).tile_state, s->width, s->height);
         rc = launch_ok("k_materialise_tiles");
     }
     s->fresh_keys = s->fresh_shadow = s->fresh_rgb = false;
@@ -172,7 +183,7 @@ int alloc_setup(SetupOut* o, uint32_t n_tri, bool with_var) {
 int reset_to_new(tr_scene* s) {
     for (uint32_t r = 0; r < s->ring; ++r) {
         s->cur = r;
-        int rc = fill_state(s, 0.0f, true, r == 0, true);
+        int rc = fill_state(s, 0.0f, true, true, true);
         if (rc) return rc;
     }
     s->cur = 0;
@@ -215,26 +226,29 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
     CU(cudaMalloc(&s->geom, g.size() * 4));
     CU(cudaMemcpy(s->geom, g.data(), g.size() * 4, cudaMemcpyHostToDevice));
     int rc;
-    if ((rc = alloc_setup(&s->cam, s->n_tri, true))) return rc;
-    if ((rc = alloc_setup(&s->lit, s->n_tri, false))) return rc;
-    s->bins.tiles_x = (s->width + kTileW - 1) / kTileW;
-    s->bins.tiles_y = (s->height + kTileH - 1) / kTileH;
-    const size_t n_tiles = (size_t)s->bins.tiles_x * s->bins.tiles_y;
-    s->bins.b.cells_x = (s->width + kCellW - 1) / kCellW;
-    s->bins.b.cells_y = (s->height + kCellH - 1) / kCellH;
-    s->bins.b.n_cells = s->bins.b.cells_x * s->bins.b.cells_y;
-    s->bins.b.parity = 0;
-    CU(cudaMalloc(&s->bins.b.count, (size_t)s->bins.b.n_cells * 2 * 4));
-    CU(cudaMemset(s->bins.b.count, 0, (size_t)s->bins.b.n_cells * 2 * 4));
-    CU(cudaMalloc(&s->bins.b.list, (size_t)s->bins.b.n_cells * kBinCap * 4));
-    s->keys.assign(s->ring, nullptr); s->rgb.assign(s->ring, nullptr); s->tile_state.assign(s->ring, nullptr);
+    s->tiles_x = (s->width + kTileW - 1) / kTileW;
+    s->tiles_y = (s->height + kTileH - 1) / kTileH;
+    const size_t n_tiles = (size_t)s->tiles_x * s->tiles_y;
+    s->slots.assign(s->ring, tr_scene::Slot{});
     for (uint32_t r = 0; r < s->ring; ++r) {
-        CU(cudaMalloc(&s->tile_state[r], n_tiles * 4));
-        CU(cudaMemset(s->tile_state[r], 0, n_tiles * 4));
-        CU(cudaMalloc(&s->keys[r], s->n_px * 8));
-        CU(cudaMalloc(&s->rgb[r], s->n_px * 3 + 16));
+        tr_scene::Slot& sl = s->slots[r];
+        if ((rc = alloc_setup(&sl.cam, s->n_tri, true))) return rc;
+        if ((rc = alloc_setup(&sl.lit, s->n_tri, false))) return rc;
+        sl.bins.cells_x = (s->width + kCellW - 1) / kCellW;
+        sl.bins.cells_y = (s->height + kCellH - 1) / kCellH;
+        sl.bins.n_cells = sl.bins.cells_x * sl.bins.cells_y;
+        sl.bins.parity = 0;
+        CU(cudaMalloc(&sl.bins.count, (size_t)sl.bins.n_cells * 2 * 4));
+        CU(cudaMemset(sl.bins.count, 0, (size_t)sl.bins.n_cells * 2 * 4));
+        CU(cudaMalloc(&sl.bins.list, (size_t)sl.bins.n_cells * kBinCap * 4));
+        CU(cudaMalloc(&sl.tile_state, n_tiles * 4));
+        CU(cudaMemset(sl.tile_state, 0, n_tiles * 4));
+        CU(cudaMalloc(&sl.keys, s->n_px * 8));
+        CU(cudaMalloc(&sl.rgb, s->n_px * 3 + 16));
+        CU(cudaMalloc(&sl.shadow, s->n_px * 4));
+        CU(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
     }
-    CU(cudaMalloc(&s->shadow, s->n_px * 4));
     CU(cudaMalloc(&s->ao, s->n_px * 4));
     CU(cudaMemset(s->ao, 0, s->n_px * 4));
     CU(cudaMalloc(&s->diag, D_COUNT * 8));
@@ -243,6 +257,7 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
     for (int k = 0; k < 4; ++k) if ((rc = upload_map(s, k, *imgs[k]))) return rc;
     CU(cudaEventCreate(&s->ev_begin));
     CU(cudaEventCreate(&s->ev_end));
+    CU(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
     if ((rc = reset_to_new(s))) return rc;
     CU(cudaStreamSynchronize(s->stream));
     return TR_OK;
@@ -256,17 +271,19 @@ void destroy_impl(tr_scene* s) {
     for (auto e : s->event_pool) cudaEventDestroy(e);
     if (s->ev_begin) cudaEventDestroy(s->ev_begin);
     if (s->ev_end) cudaEventDestroy(s->ev_end);
+    if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     for (int k = 0; k < 4; ++k) {
         if (s->maps.tex[k]) cudaDestroyTextureObject(s->maps.tex[k]);
         if (s->arrays[k]) cudaFreeArray(s->arrays[k]);
     }
-    for (auto p : s->keys) cudaFree(p);
-    for (auto p : s->tile_state) cudaFree(p);
-    for (auto p : s->rgb) cudaFree(p);
-    cudaFree(s->geom); cudaFree(s->cam.rec); cudaFree(s->cam.var); cudaFree(s->cam.bbox);
-    cudaFree(s->lit.rec); cudaFree(s->lit.bbox);
-    cudaFree(s->bins.b.count); cudaFree(s->bins.b.list);
-    cudaFree(s->shadow); cudaFree(s->ao); cudaFree(s->diag); cudaFree(s->d_checksums); cudaFree(s->scratch);
+    for (auto& sl : s->slots) {
+        if (sl.stream) { cudaStreamSynchronize(sl.stream); cudaStreamDestroy(sl.stream); }
+        if (sl.done) cudaEventDestroy(sl.done);
+        cudaFree(sl.keys); cudaFree(sl.tile_state); cudaFree(sl.rgb); cudaFree(sl.shadow);
+        cudaFree(sl.cam.rec); cudaFree(sl.cam.var); cudaFree(sl.cam.bbox); cudaFree(sl.lit.rec); cudaFree(sl.lit.bbox);
+        cudaFree(sl.bins.count); cudaFree(sl.bins.list);
+    }
+    cudaFree(s->geom); cudaFree(s->ao); cudaFree(s->diag); cudaFree(s->d_checksums); cudaFree(s->scratch);
     if (s->own_stream) cudaStreamDestroy(s->own_stream);
     delete s;
 }
@@ -277,19 +294,19 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     if (s->n_tri == 0) return TR_OK;
     Scoped sp(s, KS_SETUP);
     dim3 grid((s->n_tri + 127) / 128);
-    s->bins.b.parity ^= 1u;                 // this pass fills the other counter set; the kernel zeroes the one just used
-    s->cam.bins = s->bins.b;
-    s->lit.bins = s->bins.b;
-    if (light_pass) k_vertex_setup<true><<<grid, 128, 0, s->stream>>>(s->geom, s->lit, u, s->pipeline, s->diag);
-    else k_vertex_setup<false><<<grid, 128, 0, s->stream>>>(s->geom, s->cam, u, s->pipeline, s->diag);
+    S(s).bins.parity ^= 1u;                 // this pass fills the other counter set; the kernel zeroes the one just used
+    S(s).cam.bins = S(s).bins;
+    S(s).lit.bins = S(s).bins;
+    if (light_pass) k_vertex_setup<true><<<grid, 128, 0, s->stream>>>(s->geom, S(s).lit, u, s->pipeline, s->diag);
+    else k_vertex_setup<false><<<grid, 128, 0, s->stream>>>(s->geom, S(s).cam, u, s->pipeline, s->diag);
     return launch_ok("k_vertex_setup");
 }
 
 ShadeArgs shade_args(tr_scene* s, bool fresh_rgb) {
     ShadeArgs a{};
-    a.keys = s->keys[s->cur]; a.tile_state = s->tile_state[s->cur]; a.tiles_x = s->bins.tiles_x;
-    a.rec = s->cam.rec; a.var = s->cam.var; a.shadow = s->shadow;
-    a.rgb = s->rgb[s->cur]; a.ao_accum = s->ao; a.diag = s->diag; a.maps = s->maps; a.fresh = fresh_rgb ? 1 : 0;
+    a.keys = S(s).keys; a.tile_state = S(s).tile_state; a.tiles_x = s->tiles_x;
+    a.rec = S(s).cam.rec; a.var = S(s).cam.var; a.shadow = S(s).shadow;
+    a.rgb = S(s).rgb; a.ao_accum = s->ao; a.diag = s->diag; a.maps = s->maps; a.fresh = fresh_rgb ? 1 : 0;
     return a;
 }
 
@@ -297,14 +314,14 @@ ShadeArgs shade_args(tr_scene* s, bool fresh_rgb) {
 int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms& u, bool fresh_rgb) {
     const bool depth_only = mode == kModeDepthOnly;
     RasterArgs a{};
-    a.rec = depth_only ? s->lit.rec : s->cam.rec;
-    a.bbox = depth_only ? s->lit.bbox : s->cam.bbox;
-    a.bins = s->bins.b;
-    a.n_triangles = s->n_tri; a.width = s->width; a.height = s->height; a.tiles_x = s->bins.tiles_x;
+    a.rec = depth_only ? S(s).lit.rec : S(s).cam.rec;
+    a.bbox = depth_only ? S(s).lit.bbox : S(s).cam.bbox;
+    a.bins = S(s).bins;
+    a.n_triangles = s->n_tri; a.width = s->width; a.height = s->height; a.tiles_x = s->tiles_x;
     a.epoch = epoch; a.fresh = fresh ? 1 : 0;
-    a.keys = s->keys[s->cur]; a.tile_state = s->tile_state[s->cur]; a.depth = s->shadow; a.diag = s->diag;
+    a.keys = S(s).keys; a.tile_state = S(s).tile_state; a.depth = S(s).shadow; a.diag = s->diag;
     ShadeArgs sa = shade_args(s, fresh_rgb);
-    dim3 grid(s->bins.tiles_x, s->bins.tiles_y);
+    dim3 grid(s->tiles_x, s->tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
 #define TR_RASTER(M) k_raster<M><<<grid, kRasterThreads, 0, s->stream>>>(a, sa, u)
     switch (mode) {
@@ -452,7 +469,7 @@ int tr_scene_get_frame_buffer(tr_scene* s, uint8_t* dst) {
     CU(cudaSetDevice(s->device));
     int rc = materialise(s);
     if (rc) return rc;
-    CU(cudaMemcpyAsync(dst, s->rgb[s->cur], s->n_px * 3, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaMemcpyAsync(dst, S(s).rgb, s->n_px * 3, cudaMemcpyDeviceToHost, s->stream));
     CU(cudaStreamSynchronize(s->stream));
     return TR_OK;
 }
@@ -465,7 +482,7 @@ int tr_scene_read_frame_raw(tr_scene* s, uint8_t* dst) {
     if (rc) return rc;
     if ((rc = ensure_scratch(s, s->n_px * 3))) return rc;
     size_t n = s->n_px * 3;
-    k_flip_rows<<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(s->rgb[s->cur], s->scratch, s->width * 3, s->height);
+    k_flip_rows<<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(S(s).rgb, s->scratch, s->width * 3, s->height);
     if ((rc = launch_ok("k_flip_rows"))) return rc;
     CU(cudaMemcpyAsync(dst, s->scratch, n, cudaMemcpyDeviceToHost, s->stream));
     CU(cudaStreamSynchronize(s->stream));
@@ -478,7 +495,7 @@ static int gray_view(tr_scene* s, uint8_t* dst, bool shadow) {
     int rc = materialise(s);
     if (rc) return rc;
     if ((rc = ensure_scratch(s, s->n_px * 3))) return rc;
-    k_gray_view<<<(unsigned)((s->n_px + 255) / 256), 256, 0, s->stream>>>(shadow ? nullptr : s->keys[s->cur], s->shadow, s->scratch, s->width, s->height);
+    k_gray_view<<<(unsigned)((s->n_px + 255) / 256), 256, 0, s->stream>>>(shadow ? nullptr : S(s).keys, S(s).shadow, s->scratch, s->width, s->height);
     if ((rc = launch_ok("k_gray_view"))) return rc;
     CU(cudaMemcpyAsync(dst, s->scratch, s->n_px * 3, cudaMemcpyDeviceToHost, s->stream));
     CU(cudaStreamSynchronize(s->stream));
@@ -492,7 +509,7 @@ static int read_unpacked(tr_scene* s, float* depth, uint32_t* tri) {
     int rc = materialise(s);
     if (rc) return rc;
     if ((rc = ensure_scratch(s, s->n_px * 4))) return rc;
-    k_unpack_keys<<<(unsigned)((s->n_px + 255) / 256), 256, 0, s->stream>>>(s->keys[s->cur], depth ? (float*)s->scratch : nullptr,
+    k_unpack_keys<<<(unsigned)((s->n_px + 255) / 256), 256, 0, s->stream>>>(S(s).keys, depth ? (float*)s->scratch : nullptr,
                                                                          tri ? (uint32_t*)s->scratch : nullptr, s->n_px);
     if ((rc = launch_ok("k_unpack_keys"))) return rc;
     CU(cudaMemcpyAsync(depth ? (void*)depth : (void*)tri, s->scratch, s->n_px * 4, cudaMemcpyDeviceToHost, s->stream));
@@ -508,7 +525,7 @@ int tr_scene_read_shadow(tr_scene* s, float* dst) {
     CU(cudaSetDevice(s->device));
     int rc = materialise(s);
     if (rc) return rc;
-    CU(cudaMemcpyAsync(dst, s->shadow, s->n_px * 4, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaMemcpyAsync(dst, S(s).shadow, s->n_px * 4, cudaMemcpyDeviceToHost, s->stream));
     CU(cudaStreamSynchronize(s->stream));
     return TR_OK;
 }
@@ -537,7 +554,7 @@ int tr_scene_device_frame(tr_scene* s, void** p) {
     if (!p) return fail(TR_ERR_INVALID_ARGUMENT, "null destination");
     CU(cudaSetDevice(s->device));
     int rc = materialise(s);
-    *p = s->rgb[s->cur];
+    *p = S(s).rgb;
     return rc;
 }
 
