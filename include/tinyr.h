@@ -111,6 +111,13 @@ int tr_scene_render_ao(tr_scene* s, const float* light_dirs_xyz, uint32_t n_ligh
 int tr_scene_ao_device_buffer(tr_scene* s, void** device_ptr_u32, size_t* n_elements);
 int tr_scene_read_ao(tr_scene* s, uint32_t* accum_host);
 uint64_t tr_checksum_rgb8(const uint8_t* rgb8, size_t n_bytes);                  /* host twin of the device checksum */
+/* Deterministic light set for tr_scene_render_ao (host only): SplitMix64(seed) -> uniform sphere directions, computed
+ * in double and rounded to f32, rejecting directions on which the reference's occlusion pipeline panics or reads
+ * its shadow buffer on the wrong row: light parallel to `up` (shader.rs:194), light == -z (shader.rs:921), any model
+ * vertex outside |ndc| <= ndc_margin in the light's view (shader.rs:774-778, 909-912, 932-935; use 0.97).
+ * n_drawn (optional) receives the number of candidates drawn. */
+int tr_ao_generate_lights(const float* positions_xyz, uint32_t n_positions, const float look_at[3], const float up[3],
+                          uint64_t seed, uint32_t n_lights, float ndc_margin, float* out_dirs_xyz, uint64_t* n_drawn);
 
 /* ---- device plumbing -------------------------------------------------------------------------------- */
 int tr_device_count(int* n);

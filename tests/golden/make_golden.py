@@ -13,6 +13,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 
 import numpy as np  # noqa: E402
 
@@ -59,3 +60,8 @@ if __name__ == "__main__":
         json.dump(res, f, indent=1)
     for r in res:
         print(r["case"], r["covered"], r["frame_topdown"][:12])
+    # config 4 light set: the accepted directions are part of the fixture
+    import tiny_renderer_b200 as tr  # noqa: E402  (host-only entry point: no GPU needed)
+    lights, drawn = tr.generate_ao_lights(assets.load_model_py("diablo").positions, 1024)
+    np.save(os.path.join(HERE, "ao_lights_diablo_1024.npy"), lights)
+    print("ao lights: 1024 accepted of", drawn)

@@ -101,6 +101,7 @@ def lib():
             "tr_load_obj": [ctypes.c_char_p, ctypes.POINTER(_Mesh)], "tr_load_tga": [ctypes.c_char_p, ctypes.POINTER(_Pixels)],
             "tr_write_tga": [ctypes.c_char_p, vp, u32, u32, i32],
             "tr_scene_create_from_dir": [ctypes.POINTER(vp), ctypes.c_char_p, ctypes.c_char_p, u32, u32, ctypes.c_int32, u32],
+            "tr_ao_generate_lights": [vp, u32, vp, vp, ctypes.c_uint64, u32, ctypes.c_float, vp, ctypes.POINTER(ctypes.c_uint64)],
         }
         for name, argtypes in sig.items():
             fn = getattr(L, name)
@@ -127,4 +128,5 @@ def _f3(v):
     return np.ascontiguousarray(np.asarray(v, dtype=np.float32).reshape(3))
 
 
-from .scene import Scene, load_obj, load_tga, write_tga, load_model_dir, checksum_rgb8, device_count, pinned_empty  # noqa: E402,F401
+from .scene import (Scene, Model, load_obj, load_tga, write_tga, load_model_dir, checksum_rgb8, device_count, pinned_empty,  # noqa: E402,F401
+                    generate_ao_lights, AO_LIGHT_SEED, AO_NDC_MARGIN)

@@ -67,6 +67,21 @@ def checksum_rgb8(img):
     return int(lib().tr_checksum_rgb8(a.ctypes.data, a.size))
 
 
+AO_LIGHT_SEED = 0x5EED0A0
+AO_NDC_MARGIN = 0.97
+
+
+def generate_ao_lights(positions, n_lights, seed=AO_LIGHT_SEED, look_at=(0.0, 0.0, 0.0), up=(0.0, 1.0, 0.0), ndc_margin=AO_NDC_MARGIN):
+    """Deterministic light directions for Scene.render_ao (tr_ao_generate_lights): (n, 3) f32 and the draw count."""
+    pos = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+    out = np.zeros((int(n_lights), 3), np.float32)
+    drawn = ctypes.c_uint64(0)
+    at, upv = _f3(look_at), _f3(up)          # keep the arrays alive across the call
+    _check(lib().tr_ao_generate_lights(pos.ctypes.data, len(pos), at.ctypes.data, upv.ctypes.data, int(seed),
+                                       int(n_lights), float(ndc_margin), out.ctypes.data, ctypes.byref(drawn)))
+    return out, int(drawn.value)
+
+
 def pinned_empty(shape, dtype):
     """numpy array over cudaMallocHost memory (fast D2H for the get_* calls).  Freed with the array."""
     dtype = np.dtype(dtype)
@@ -137,7 +152,8 @@ class Scene:
         _check(lib().tr_scene_clear(self._h))
 
     def set_light_direction(self, light_direction):
-        _check(lib().tr_scene_set_light_direction(self._h, _f3(light_direction).ctypes.data))
+        d = _f3(light_direction)
+        _check(lib().tr_scene_set_light_direction(self._h, d.ctypes.data))
 
     def set_camera(self, look_from, look_at, up):
         a, b, c = _f3(look_from), _f3(look_at), _f3(up)
