@@ -28,6 +28,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 W4K, H4K = 3840, 2160
+METRIC = "Mpixels/s shaded (device-timed) at 3840x2160"
 PIPES = ("phong", "darboux")
 N_ANGLES = 8
 LIGHT_ANGLE = 0.7
@@ -61,38 +62,44 @@ def view_batch(rank=0):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (recipe in B200_PROFILING.md)."""
-    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
-        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    """SM clock and throttle reasons DURING the timed region, sampled through NVML from a thread every ~2 ms
+    (the timed region of a default run is well under a second, too short for `nvidia-smi -lms`)."""
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.thread, self.stop_flag, self.max_mhz = index, [], None, False, None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
-            threading.Thread(target=self._pump, daemon=True).start()
-        except OSError:
-            self.proc = None
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            return
 
-    def _pump(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+        def pump():
+            while not self.stop_flag:
+                try:
+                    self.rows.append((pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM),
+                                      pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)))
+                except Exception:
+                    pass
+                time.sleep(0.002)
+
+        self.thread = threading.Thread(target=pump, daemon=True)
+        self.thread.start()
 
     def stop(self):
-        if self.proc:
-            self.proc.terminate()
-            try:
-                self.proc.wait(timeout=5)
-            except subprocess.TimeoutExpired:
-                self.proc.kill()
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
-        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        self.stop_flag = True
+        if self.thread:
+            self.thread.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows]
+        mask = 0
+        for r in self.rows:
+            mask |= int(r[1])
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": [n for n, bit in self.REASONS if mask & bit], "samples": len(sm)}
 
 
 # ---- CPU side: the reference's own CPU path, as restated by the oracle (Rust cannot be compiled here) --------
@@ -145,7 +152,10 @@ def run_reference(args, rank, world):
     model, data = bench_model()
     cores = os.cpu_count() or 1
     views = view_batch()
-    jobs = [(p, views[k]) for p in PIPES for k in range(N_ANGLES)]       # one full step = 16 frames
+    # One reference step = a bounded sample of the GPU arm's step (16 frames): 2 of the 8 views of each pipeline, so
+    # that any --steps K the driver passes ends within minutes (a 4K frame costs ~0.15-0.5 s of one host core).
+    sample_views = 2
+    jobs = [(p, views[k]) for p in PIPES for k in range(sample_views)]
     threads = min(cores, len(jobs))
     times = []
     for i in range(args.warmup + args.steps):
@@ -154,12 +164,13 @@ def run_reference(args, rank, world):
             times.append(t)
     total = sum(times)
     value = args.steps * len(jobs) * W4K * H4K / total / 1e6
-    line = {"impl": "reference", "metric": "Mpixels/s shaded at 3840x2160", "value": value, "unit": "Mpixels/s",
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mpixels/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": data,
             "config": workload_config(),
             "cpu_baseline": {"value": value, "unit": "Mpixels/s", "cores": threads, "kind": "port",
-                             "sample": "full step: 16 frames at 3840x2160 per step over %d host threads" % threads},
+                             "sample": "%d frames per step (%d views x phong+darboux) at 3840x2160, oracle C++ port of "
+                                       "scene.rs/shader.rs, one frame per host thread, %d threads" % (len(jobs), sample_views, threads)},
             "e2e": {"value": value, "unit": "Mpixels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -194,6 +205,61 @@ def batch_roofline(us_per_frame, n_px, covered, n_tri, peak):
     return {"algorithmic_bytes_per_frame": nbytes, "us_per_frame": us_per_frame, "achieved": ach, "frac": ach / peak}
 
 
+AO_LIGHTS = 1024
+
+
+def run_ao(args, rank, world, dev, model, dist, stream):
+    """BASELINE config 4: diablo, occlusion pipeline, 1024 light-direction depth passes at 3840x2160, lights sharded
+    over the ranks (strong scaling: the light count is fixed), ONE all-reduce(sum) of the u32 accumulators at the
+    end.  Device-timed (CUDA events on the launching stream), max over ranks."""
+    import torch
+    import tiny_renderer_b200 as tr
+    from tiny_renderer_b200 import multi
+    from tiny_renderer_b200.scene import Scene
+    lights, drawn = tr.generate_ao_lights(model.positions, AO_LIGHTS)
+    s = Scene(W4K, H4K, model, "occlusion", device=dev)
+    s.set_stream(stream)
+    lf, la, up, _ = __import__("assets").view_vectors(0.0, 0.0)
+    s.set_camera(lf, la, up)
+    lo, hi = multi.shard_range(len(lights), rank, world)
+    s.render_ao(lights[lo:min(hi, lo + 8)], reset=True, read=False)          # warm-up
+    acc = multi.ao_accumulator_tensor(s)
+    if dist is not None:
+        dist.all_reduce(acc)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    e0.record()
+    s.render_ao(lights[lo:hi], reset=True, read=False)
+    e1.record()
+    multi.allreduce_ao(acc)
+    e2.record()
+    torch.cuda.synchronize()
+    ms, ar_ms = e0.elapsed_time(e2), e1.elapsed_time(e2)
+    if dist is not None:
+        t = torch.tensor([ms, ar_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ar_ms = float(t[0].item()), float(t[1].item())
+    total = s.read_ao()
+    covered = int((s.raw_visibility() != 0xFFFFFFFF).sum())
+    diag = s.diagnostics()
+    s.close()
+    n_px = W4K * H4K
+    per_pass_bytes = 8 * n_px + 8 * covered              # SURVEY.md §8(d): shadow write + one read + u32 accumulate RMW
+    peak, _ = load_peaks()
+    us_per_pass = ms * 1e3 / max(1, hi - lo)
+    return {"metric": "AO depth passes/s", "value": AO_LIGHTS / (ms * 1e-3), "unit": "passes/s", "n_gpus": world,
+            "scaling": "strong", "lights": AO_LIGHTS, "lights_per_gpu": hi - lo, "ms": ms, "allreduce_ms": ar_ms,
+            "allreduce_bytes": 4 * n_px, "us_per_pass": us_per_pass, "checksum": int(total.astype(np.uint64).sum()),
+            "shadow_index_oob": diag["shadow_index_oob"], "shadow_x_wrap": diag["shadow_x_wrap"],
+            "roofline": {"bound": "hbm", "algorithmic_bytes_per_pass": per_pass_bytes,
+                         "achieved": per_pass_bytes / (us_per_pass * 1e-6) / 1e9, "peak": peak,
+                         "frac": per_pass_bytes / (us_per_pass * 1e-6) / 1e9 / peak},
+            "config": "BASELINE config 4: diablo, occlusion, %d light directions (SplitMix64 seed 0x5EED0A0, %d drawn), "
+                      "3840x2160, camera angle 0" % (AO_LIGHTS, drawn)}
+
+
 def run_gpu(args, rank, world, local_rank):
     import torch
     import tiny_renderer_b200 as tr
@@ -205,7 +271,12 @@ def run_gpu(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = local_rank
     torch.cuda.set_device(dev)
-    stream = torch.cuda.current_stream().cuda_stream
+    # All device work of the bench (scenes, events, the NCCL all-reduce) is ordered on ONE explicit stream: a
+    # scene given the NULL stream would fall back to its own stream and escape the CUDA events below.
+    tstream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+    assert stream != 0
     model, data = bench_model()
     n_px = W4K * H4K
     n_tri = len(model.tri_idx)
@@ -270,7 +341,7 @@ def run_gpu(args, rank, world, local_rank):
         e2e_s = float(t.item())
     e2e_value = world * e2e_steps * frames_per_step * n_px / e2e_s / 1e6
 
-    line = {"metric": "Mpixels/s shaded (device-timed) at 3840x2160", "value": value, "unit": "Mpixels/s", "n_gpus": world,
+    line = {"metric": METRIC, "value": value, "unit": "Mpixels/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": data, "config": workload_config(),
             "e2e": {"value": e2e_value, "unit": "Mpixels/s", "h2d_bytes_per_step": frames_per_step * 48,
@@ -321,6 +392,7 @@ def run_gpu(args, rank, world, local_rank):
             line["cpu_baseline"] = cpu_baseline(model)
     for s in scenes.values():
         s.close()
+    line["ao"] = run_ao(args, rank, world, dev, model, dist, stream)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:
@@ -331,7 +403,7 @@ def run_gpu(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="tinyr", choices=["tinyr", "reference"])
     args = ap.parse_args()

@@ -101,7 +101,9 @@ typedef struct tr_view {
 } tr_view;
 /* For each view: set_light_direction, set_camera, clear, render (app.rs:170,208-210).  checksums (optional,
  * host, n) receives a 64-bit checksum of each top-down RGB8 frame computed on the device (see
- * tr_checksum_rgb8); frames (optional, host, n*3*w*h) receives every frame. */
+ * tr_checksum_rgb8); frames (optional, host, n*3*w*h) receives every frame.  With ring > 1 (tr_scene_desc) consecutive
+ * frames overlap on the device.  Returns after the host outputs have landed; with neither output requested the call
+ * is asynchronous on the scene stream like tr_scene_render. */
 int tr_scene_render_views(tr_scene* s, const tr_view* views, uint32_t n_views, uint64_t* checksums, uint8_t* frames_rgb8_topdown);
 /* Many-light ambient occlusion: for each light `set_light_direction; clear; render` with the occlusion
  * pipeline (shader.rs:806-963) and accum[i + j*w] += gray (u32).  Camera visibility is computed once.

@@ -146,6 +146,9 @@ def test_ao_allreduce_tensor_view(tinyr):
     assert np.array_equal(t.cpu().numpy().view(np.uint32).reshape(120, 160), ref)
     out = multi.render_ao_sharded(g, lights, 0, 1)                       # world 1: no collective
     assert np.array_equal(out, ref)
+    t.add_(3)                                                             # zero-copy: torch writes reach the scene
+    torch.cuda.synchronize()
+    assert np.array_equal(g.read_ao(), ref + 3)
     g.close()
 
 
