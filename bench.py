@@ -217,7 +217,7 @@ def run_ao(args, rank, world, dev, model, dist, stream):
     from tiny_renderer_b200 import multi
     from tiny_renderer_b200.scene import Scene
     lights, drawn = tr.generate_ao_lights(model.positions, AO_LIGHTS)
-    s = Scene(W4K, H4K, model, "occlusion", device=dev)
+    s = Scene(W4K, H4K, model, "occlusion", device=dev, ring=RING)
     s.set_stream(stream)
     lf, la, up, _ = __import__("assets").view_vectors(0.0, 0.0)
     s.set_camera(lf, la, up)

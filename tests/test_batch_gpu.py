@@ -95,7 +95,8 @@ def test_render_views_two_pass_pipeline_overlapped(tinyr, oracle):
     g.close()
 
 
-def test_ao_batch_matches_oracle_and_is_shard_invariant(tinyr, oracle):
+@pytest.mark.parametrize("ring", [1, 3])
+def test_ao_batch_matches_oracle_and_is_shard_invariant(tinyr, oracle, ring):
     """Config 4 semantics at test size: accum = sum over lights of the occlusion gray frame (u32).  GPU == oracle
     bit for bit; splitting the lights into shards and adding the shard sums gives the same buffer (what the
     all-reduce does across GPUs); the batch equals per-light occlusion renders summed."""
@@ -104,7 +105,7 @@ def test_ao_batch_matches_oracle_and_is_shard_invariant(tinyr, oracle):
     w, h = 400, 304
     lights, _ = tinyr.generate_ao_lights(m.positions, 12)
     lf, la, up, _ = assets.view_vectors(0.0, 0.0)
-    g = Scene(w, h, m, "occlusion")
+    g = Scene(w, h, m, "occlusion", ring=ring)
     g.set_camera(lf, la, up)
     total = g.render_ao(lights)
     o = oracle.OracleScene(w, h, m, "occlusion")

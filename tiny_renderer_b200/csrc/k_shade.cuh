@@ -166,7 +166,8 @@ __global__ void __launch_bounds__(kShadeThreads) k_ao_accumulate(const ShadeArgs
     float z, b0, b1, b2;
     fragment_depth(__float_as_int(r0.x), __float_as_int(r0.y), __float_as_int(r0.z), __float_as_int(r0.w),
                    __float_as_int(r1.x), __float_as_int(r1.y), r1.z, r1.w, r2.x, px, py, z, b0, b1, b2);
-    a.ao_accum[(size_t)py * u.width + px] += shade_pixel<P_OCCLUSION>(a, u, lo & kTriMask, px, py, z, b0, b1, b2) & 0xffu;
+    // integer add: the order of the light passes (which may overlap on the device) cannot change the sum
+    atomicAdd(&a.ao_accum[(size_t)py * u.width + px], shade_pixel<P_OCCLUSION>(a, u, lo & kTriMask, px, py, z, b0, b1, b2) & 0xffu);
 }
 
 }  // namespace tr

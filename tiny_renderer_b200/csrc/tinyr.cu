@@ -341,8 +341,10 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
 }
 
 // K6: deferred occlusion pass of the many-light AO batch.
-int run_ao_accumulate(tr_scene* s, const Uniforms& u) {
-    ShadeArgs a = shade_args(s, false);
+int run_ao_accumulate(tr_scene* s, const Uniforms& u, uint32_t cam_slot) {
+    ShadeArgs a = shade_args(s, false);                  // shadow buffer of the current (light) slot
+    const tr_scene::Slot& c = s->slots[cam_slot];        // visibility of the camera slot
+    a.keys = c.keys; a.tile_state = c.tile_state; a.rec = c.cam.rec; a.var = c.cam.var;
     size_t threads = (size_t)shade_threads_per_row(s->width) * s->height;
     dim3 grid((unsigned)((threads + kShadeThreads - 1) / kShadeThreads));
     Scoped sp(s, KS_AO);
