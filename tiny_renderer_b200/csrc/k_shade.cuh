@@ -47,13 +47,57 @@ __device__ __forceinline__ f3 decode_normal(uchar4 c) {
 __device__ __forceinline__ uint32_t blend_black(uint32_t c, float t) { return cast_u8(t * (float)c + (1.0f - t) * 0.0f); }
 __device__ __forceinline__ uint32_t pack_rgb(uint32_t r, uint32_t g, uint32_t b) { return r | (g << 8) | (b << 16); }
 
+// Events on which the reference panics or misreads, counted in registers and flushed once per thread.
+struct DiagLocal {
+    uint32_t w_zero = 0, xwrap = 0, oob = 0;
+    __device__ __forceinline__ void flush(unsigned long long* diag) const {
+        if (w_zero | xwrap | oob) {
+            if (w_zero) atomicAdd(&diag[D_W_ZERO], (unsigned long long)w_zero);
+            if (xwrap) atomicAdd(&diag[D_SHADOW_XWRAP], (unsigned long long)xwrap);
+            if (oob) atomicAdd(&diag[D_SHADOW_OOB], (unsigned long long)oob);
+        }
+    }
+};
+
+// `f32::round() as u32` (shader.rs:774-775): round half away from zero, then Rust's saturating cast (negative and
+// NaN -> 0).  t = trunc(x) and x - t are exact, so this equals cast_u32(roundf(x)) for every input.
+__device__ __forceinline__ uint32_t round_u32(float x) {
+    float t = truncf(x);
+    uint32_t r = __float2uint_rz(t);
+    if (x - t >= 0.5f) r += 1u;
+    return r;
+}
+
 // Shadow-buffer lookup of shader.rs:774-778 / 909-912 / 932-935: round, saturating cast, wrapping u32 index.
-__device__ __forceinline__ float shadow_lookup(const float* shadow, f3 s, uint32_t width, uint32_t n_px, unsigned long long* diag) {
-    uint32_t sx = cast_u32(roundf(s.x)), sy = cast_u32(roundf(s.y));
-    if (sx >= width) atomicAdd(&diag[D_SHADOW_XWRAP], 1ull);
+__device__ __forceinline__ float shadow_lookup(const float* shadow, f3 s, uint32_t width, uint32_t n_px, DiagLocal& dl) {
+    uint32_t sx = round_u32(s.x), sy = round_u32(s.y);
+    dl.xwrap += sx >= width ? 1u : 0u;
     uint32_t idx = sx + sy * width;
-    if (idx >= n_px) { atomicAdd(&diag[D_SHADOW_OOB], 1ull); return -3.402823466e38f; }
+    if (idx >= n_px) { dl.oob += 1u; return -3.402823466e38f; }
     return __ldg(&shadow[idx]);
+}
+
+// Occlusion fragment (shader.rs:886-947) for a pixel whose depth z and world position wp = from_homogeneous(i_vpmv *
+// (px, py, z, 1)) are known; returns the gray level.
+__device__ __forceinline__ uint32_t occlusion_gray(const float* shadow, const Uniforms& u, int px, int py, float z, f3 wp, DiagLocal& dl) {
+    const uint32_t n_px = u.width * u.height;
+    bool ok;
+    f3 fs = dehomog(xform(u.shadow_from_screen, f4{(float)px, (float)py, z, 1.0f}), ok);
+    dl.w_zero += ok ? 0u : 1u;
+    float fsv = shadow_lookup(shadow, fs, u.width, n_px, dl);
+    float occ = 1.0f;
+#pragma unroll 4
+    for (int k = 0; k < 16; ++k) {
+        f3 sp = wp + u.ao_step[k];
+        f3 sc = dehomog(xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f}), ok);
+        dl.w_zero += ok ? 0u : 1u;
+        float sv = shadow_lookup(shadow, sc, u.width, n_px, dl);
+        if (sv - 1.0f > fsv) {
+            float strength = fminf((sv - fsv) / 20.0f, 1.0f);
+            occ -= 0.0625f * strength;
+        }
+    }
+    return cast_u8(occ * 255.0f + (1.0f - occ) * 0.0f);
 }
 
 // Fragment math of one pipeline for one covered pixel; returns packed RGB.  z and (b0, b1, b2) are the depth and the
@@ -69,27 +113,12 @@ __device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Unifor
 
     if (PIPE == P_OCCLUSION) {
         // shader.rs:882-947 with the per-pass constants hoisted into Uniforms by K0
-        const uint32_t n_px = u.width * u.height;
-        f4 frag{(float)px, (float)py, z, 1.0f};
-        bool ok1, ok2;
-        f3 wp = dehomog(xform(u.i_vpmv, frag), ok1);
-        f3 fs = dehomog(xform(u.shadow_from_screen, frag), ok2);
-        if (!ok1 || !ok2) atomicAdd(&a.diag[D_W_ZERO], 1ull);
-        float fsv = shadow_lookup(a.shadow, fs, u.width, n_px, a.diag);
-        float occ = 1.0f;
-#pragma unroll 4
-        for (int k = 0; k < 16; ++k) {
-            f3 sp = wp + u.ao_step[k];
-            bool ok;
-            f3 sc = dehomog(xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f}), ok);
-            if (!ok) atomicAdd(&a.diag[D_W_ZERO], 1ull);
-            float sv = shadow_lookup(a.shadow, sc, u.width, n_px, a.diag);
-            if (sv - 1.0f > fsv) {
-                float strength = fminf((sv - fsv) / 20.0f, 1.0f);
-                occ -= 0.0625f * strength;
-            }
-        }
-        uint32_t g = cast_u8(occ * 255.0f + (1.0f - occ) * 0.0f);
+        DiagLocal dl;
+        bool ok;
+        f3 wp = dehomog(xform(u.i_vpmv, f4{(float)px, (float)py, z, 1.0f}), ok);
+        dl.w_zero += ok ? 0u : 1u;
+        uint32_t g = occlusion_gray(a.shadow, u, px, py, z, wp, dl);
+        dl.flush(a.diag);
         return pack_rgb(g, g, g);
     }
 
@@ -102,9 +131,11 @@ __device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Unifor
         diff = (b0 * in.x + b1 * in.y) + b2 * in.z;                              // shader.rs:397, 784
         if (PIPE == P_SHADOW) {
             bool ok;
+            DiagLocal dl;
             f3 s = dehomog(xform(u.shadow_from_screen, f4{(float)px, (float)py, z, 1.0f}), ok);
-            if (!ok) atomicAdd(&a.diag[D_W_ZERO], 1ull);
-            float sv = shadow_lookup(a.shadow, s, u.width, u.width * u.height, a.diag);
+            dl.w_zero += ok ? 0u : 1u;
+            float sv = shadow_lookup(a.shadow, s, u.width, u.width * u.height, dl);
+            dl.flush(a.diag);
             float coef = (s.z + 1.0f < sv) ? 0.3f : 1.0f;                         // shader.rs:776-780
             diff = diff * coef;
         }
@@ -146,28 +177,62 @@ __device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Unifor
     return pack_rgb(blend_black(c.x, diff), blend_black(c.y, diff), blend_black(c.z, diff));
 }
 
-// K6 ao_accumulate — deferred occlusion pass of the many-light AO batch: adds the occlusion gray of every covered
-// pixel into ao_accum (u32, bottom-up).  One thread per pixel; a warp covers 32 consecutive pixels of one row (rows
-// are padded to a multiple of 32 threads), which always lie inside one raster tile.
+// K6 — many-light ambient occlusion (BASELINE config 4).  The camera's visibility does not depend on the light, so
+// the batch first compacts the covered pixels once (k_ao_compact: pixel coordinates, depth and world position of the
+// winning fragment — everything of shader.rs:886-905 that is light-independent) and then runs one k_ao_accumulate per
+// light over that list only: fully populated warps, no key / tile-state traffic, 20 bytes read per covered pixel.
 constexpr int kShadeThreads = 256;
-__host__ __device__ inline uint32_t shade_threads_per_row(uint32_t width) { return (width + 31u) & ~31u; }
 
-__global__ void __launch_bounds__(kShadeThreads) k_ao_accumulate(const ShadeArgs a, const Uniforms u) {
-    const uint32_t tpr = shade_threads_per_row(u.width);
-    const size_t gid = (size_t)blockIdx.x * kShadeThreads + threadIdx.x;
-    const int py = (int)(gid / tpr), px = (int)(gid % tpr);
-    if (py >= (int)u.height || px >= (int)u.width) return;
-    // A cleared tile has no winners and its keys are stale.
-    if (a.tile_state[(uint32_t)(py / kTileH) * a.tiles_x + (uint32_t)(px / kTileW)] != 0u) return;
-    const uint32_t lo = key_lo(__ldg(&a.keys[(size_t)py * u.width + px]));
-    if (lo == kNoTri || (lo >> 24) != 0u) return;
-    const float4* r = a.rec + (size_t)(lo & kTriMask) * 4;
-    float4 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
-    float z, b0, b1, b2;
-    fragment_depth(__float_as_int(r0.x), __float_as_int(r0.y), __float_as_int(r0.z), __float_as_int(r0.w),
-                   __float_as_int(r1.x), __float_as_int(r1.y), r1.z, r1.w, r2.x, px, py, z, b0, b1, b2);
+struct AoList {
+    float4* frag;          // wp.x wp.y wp.z z
+    uint32_t* pix;         // px | py << 16
+    uint32_t* count;       // device counter (entries appended)
+};
+
+__global__ void __launch_bounds__(kShadeThreads) k_ao_compact(const ShadeArgs a, const Uniforms u, AoList out) {
+    const int px = (int)(blockIdx.x * kShadeThreads + threadIdx.x), py = (int)blockIdx.y;
+    bool covered = false;
+    float4 frag = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    // A cleared tile has no winners and its keys are stale.  (A warp's 32 pixels lie in one raster tile.)
+    if (px < (int)u.width && a.tile_state[(uint32_t)(py / kTileH) * a.tiles_x + (uint32_t)(px / kTileW)] == 0u) {
+        const uint32_t lo = key_lo(__ldg(&a.keys[(size_t)py * u.width + px]));
+        if (lo != kNoTri && (lo >> 24) == 0u) {
+            const float4* r = a.rec + (size_t)(lo & kTriMask) * 4;
+            float4 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
+            float z, b0, b1, b2;
+            fragment_depth(__float_as_int(r0.x), __float_as_int(r0.y), __float_as_int(r0.z), __float_as_int(r0.w),
+                           __float_as_int(r1.x), __float_as_int(r1.y), r1.z, r1.w, r2.x, px, py, z, b0, b1, b2);
+            bool ok;
+            f3 wp = dehomog(xform(u.i_vpmv, f4{(float)px, (float)py, z, 1.0f}), ok);
+            if (!ok) atomicAdd(&a.diag[D_W_ZERO], 1ull);      // from_homogeneous(i_vpmv * ..) with w == 0: shader.rs:890 panics
+            frag = make_float4(wp.x, wp.y, wp.z, z);
+            covered = true;
+        }
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, covered);
+    if (m == 0u) return;
+    const int lane = threadIdx.x & 31;
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(out.count, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (covered) {
+        const uint32_t i = base + __popc(m & ((1u << lane) - 1u));
+        out.frag[i] = frag;
+        out.pix[i] = (uint32_t)px | ((uint32_t)py << 16);
+    }
+}
+
+__global__ void __launch_bounds__(kShadeThreads) k_ao_accumulate(const ShadeArgs a, const Uniforms u, const AoList in, uint32_t n) {
+    const uint32_t i = blockIdx.x * kShadeThreads + threadIdx.x;
+    if (i >= n) return;
+    const float4 frag = __ldg(&in.frag[i]);
+    const uint32_t pix = __ldg(&in.pix[i]);
+    const int px = (int)(pix & 0xffffu), py = (int)(pix >> 16);
+    DiagLocal dl;
+    const uint32_t g = occlusion_gray(a.shadow, u, px, py, frag.w, f3{frag.x, frag.y, frag.z}, dl);
+    dl.flush(a.diag);
     // integer add: the order of the light passes (which may overlap on the device) cannot change the sum
-    atomicAdd(&a.ao_accum[(size_t)py * u.width + px], shade_pixel<P_OCCLUSION>(a, u, lo & kTriMask, px, py, z, b0, b1, b2) & 0xffu);
+    atomicAdd(&a.ao_accum[(size_t)py * u.width + px], g);
 }
 
 }  // namespace tr

@@ -55,6 +55,8 @@ struct tr_scene {
     std::vector<Slot> slots;
     uint32_t tiles_x = 0, tiles_y = 0;
     uint32_t* ao = nullptr;
+    AoList ao_list{};                  // covered pixels of the camera view (many-light AO batch), allocated on first use
+    uint32_t ao_list_n = 0;
     unsigned long long* diag = nullptr;
     unsigned long long* d_checksums = nullptr; size_t checksum_cap = 0;
     uint8_t* scratch = nullptr; size_t scratch_bytes = 0;
@@ -283,7 +285,7 @@ void destroy_impl(tr_scene* s) {
         cudaFree(sl.cam.rec); cudaFree(sl.cam.var); cudaFree(sl.cam.bbox); cudaFree(sl.lit.rec); cudaFree(sl.lit.bbox);
         cudaFree(sl.bins.count); cudaFree(sl.bins.list);
     }
-    cudaFree(s->geom); cudaFree(s->ao); cudaFree(s->diag); cudaFree(s->d_checksums); cudaFree(s->scratch);
+    cudaFree(s->geom); cudaFree(s->ao); cudaFree(s->ao_list.frag); cudaFree(s->ao_list.pix); cudaFree(s->ao_list.count); cudaFree(s->diag); cudaFree(s->d_checksums); cudaFree(s->scratch);
     if (s->own_stream) cudaStreamDestroy(s->own_stream);
     delete s;
 }
@@ -341,14 +343,34 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
 }
 
 // K6: deferred occlusion pass of the many-light AO batch.
-int run_ao_accumulate(tr_scene* s, const Uniforms& u, uint32_t cam_slot) {
+// K6 part 1: compact the covered pixels of the camera slot (depth + world position), once per AO batch.
+int run_ao_compact(tr_scene* s, const Uniforms& u) {
+    if (!s->ao_list.frag) {
+        CU(cudaMalloc(&s->ao_list.frag, s->n_px * sizeof(float4)));
+        CU(cudaMalloc(&s->ao_list.pix, s->n_px * 4));
+        CU(cudaMalloc(&s->ao_list.count, 4));
+    }
+    CU(cudaMemsetAsync(s->ao_list.count, 0, 4, s->stream));
+    ShadeArgs a = shade_args(s, false);
+    dim3 grid((s->width + kShadeThreads - 1) / kShadeThreads, s->height);
+    {
+        Scoped sp(s, KS_AO);
+        k_ao_compact<<<grid, kShadeThreads, 0, s->stream>>>(a, u, s->ao_list);
+    }
+    int rc = launch_ok("k_ao_compact");
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(&s->ao_list_n, s->ao_list.count, 4, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));       // the per-light grids are sized by the count
+    return TR_OK;
+}
+
+// K6 part 2: one light's occlusion term for every covered pixel, added into the accumulator.
+int run_ao_accumulate(tr_scene* s, const Uniforms& u) {
+    if (s->ao_list_n == 0) return TR_OK;
     ShadeArgs a = shade_args(s, false);                  // shadow buffer of the current (light) slot
-    const tr_scene::Slot& c = s->slots[cam_slot];        // visibility of the camera slot
-    a.keys = c.keys; a.tile_state = c.tile_state; a.rec = c.cam.rec; a.var = c.cam.var;
-    size_t threads = (size_t)shade_threads_per_row(s->width) * s->height;
-    dim3 grid((unsigned)((threads + kShadeThreads - 1) / kShadeThreads));
+    dim3 grid((s->ao_list_n + kShadeThreads - 1) / kShadeThreads);
     Scoped sp(s, KS_AO);
-    k_ao_accumulate<<<grid, kShadeThreads, 0, s->stream>>>(a, u);
+    k_ao_accumulate<<<grid, kShadeThreads, 0, s->stream>>>(a, u, s->ao_list, s->ao_list_n);
     return launch_ok("k_ao_accumulate");
 }
 
