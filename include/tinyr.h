@@ -131,6 +131,9 @@ int tr_scene_timer_end(tr_scene* s, float* elapsed_ms);                         
  * K3 raster_visibility, K4 shadow_depth, K5 shade, K6 ao_accumulate, K7 clear/pack, K8 checksum. */
 int tr_scene_set_profiling(tr_scene* s, int enabled);
 int tr_scene_kernel_times(tr_scene* s, float total_ms[8], uint64_t launches[8]);
+/* Device self-test of the rasteriser's 3-instruction exact division (k_tile.cuh exact_quotient) against IEEE f32
+ * division over n_pairs pseudo-random integer pairs 0 <= a <= b <= 2^21; *mismatches must come back 0. */
+int tr_selftest_exact_quotient(int device, uint64_t n_pairs, uint64_t seed, uint64_t* mismatches);
 void* tr_host_alloc(size_t bytes);                                                /* pinned host memory for fast get_* copies */
 void tr_host_free(void* p);
 

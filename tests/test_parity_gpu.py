@@ -130,3 +130,13 @@ def test_error_codes(tinyr):
     with pytest.raises(tinyr.TinyrError) as e:
         s.render()
     assert e.value.name == "TR_ERR_REFERENCE_UNDEFINED"
+
+
+def test_exact_quotient_selftest(tinyr):
+    """The 3-instruction division used for the barycentrics (integer operands, |cz| <= 2^21; proof in DESIGN.md §4)
+    against IEEE division on 2^31 pseudo-random and adversarial pairs: zero mismatching bit patterns."""
+    import ctypes
+    bad = ctypes.c_uint64(123)
+    for seed in (1, 0xDEADBEEF):
+        rc = tinyr.lib().tr_selftest_exact_quotient(0, 1 << 30, seed, ctypes.byref(bad))
+        assert rc == 0 and bad.value == 0, (rc, bad.value)

@@ -57,6 +57,30 @@ __global__ void __launch_bounds__(256) k_flip_rows(const uint8_t* src, uint8_t* 
     dst[(size_t)(h - 1 - y) * row_bytes + b] = src[i];
 }
 
+// Self-test of exact_quotient() (k_tile.cuh) against the IEEE division it replaces: random and adversarial integer
+// pairs 0 <= a <= b <= 2^21.  Counts mismatching bit patterns.
+__global__ void __launch_bounds__(256) k_selftest_quotient(unsigned long long n, unsigned long long seed, unsigned long long* mismatches) {
+    unsigned long long i0 = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x, stride = (unsigned long long)gridDim.x * blockDim.x;
+    unsigned long long bad = 0;
+    for (unsigned long long i = i0; i < n; i += stride) {
+        unsigned long long z = seed + (i + 1ull) * 0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        uint32_t b = (uint32_t)(z & 0x1FFFFFu) + 1u;                       // 1 .. 2^21
+        if ((i & 7ull) == 0ull) b = 0x200000u - (uint32_t)((z >> 40) & 0xFFu);   // near the top of the range
+        if ((i & 7ull) == 1ull) b = (1u << ((z >> 50) % 22u)) + (uint32_t)((z >> 56) & 3u);   // near powers of two
+        if (b > 0x200000u) b = 0x200000u;
+        uint32_t a = (uint32_t)((z >> 21) % (unsigned long long)(b + 1u));      // 0 .. b
+        if ((i & 15ull) == 2ull) a = b - (uint32_t)((z >> 60) & 3u) > b ? b : b - (uint32_t)((z >> 60) & 3u);
+        float fa = (float)a, fb = (float)b;
+        float q_ref = fa / fb;
+        float q = exact_quotient(fa, fb, 1.0f / fb);
+        bad += __float_as_uint(q) != __float_as_uint(q_ref) ? 1ull : 0ull;
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
+
 // K8: position-weighted 64-bit checksum of a byte image viewed as little-endian u32 words:
 // sum_i word_i * (2 i + 1) mod 2^64 (tr_checksum_rgb8 is the host twin).  n_words = bytes / 4 (bytes % 4 == 0).
 __global__ void __launch_bounds__(256) k_checksum(const uint32_t* words, size_t n_words, unsigned long long* out) {

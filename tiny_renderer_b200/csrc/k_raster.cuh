@@ -73,7 +73,7 @@ __device__ __forceinline__ void stage_polygon(const RasterArgs& a, uint32_t t, i
         d[0] = make_int4(x0, y0, x1, y1);
         d[1] = make_int4(x2, y2, 0, (int)(id | kInexactFlag));
     }
-    d[2] = make_int4(__float_as_int(r1.z), __float_as_int(r1.w), __float_as_int(r2.x), 0);
+    d[2] = make_int4(__float_as_int(r1.z), __float_as_int(r1.w), __float_as_int(r2.x), __float_as_int(1.0f / fabsf((float)d[1].z)));
     s_lo[slot] = lo;
     s_hi[slot] = hi;
 }
@@ -146,11 +146,15 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a, c
         touched = true;
 
         // ---- (2) warps pull 8x4 blocks off the tile; ballot the staged bboxes against the block, evaluate per pixel ----
+#ifdef TR_STATIC_BLOCKS
+        for (int blk = warp; blk < kBlocks; blk += kRasterThreads / 32) {
+#else
         for (;;) {
             int blk = 0;
             if (lane == 0) blk = atomicAdd(&s_block, 1);
             blk = __shfl_sync(0xffffffffu, blk, 0);
             if (blk >= kBlocks) break;
+#endif
             const int bx0 = (blk % kBlocksX) * 8, by0 = (blk / kBlocksX) * 4;   // tile-relative
             const int lx = bx0 + (lane & 7), ly = by0 + (lane >> 3);
             const int px = tx0 + lx, py = ty0 + ly;
@@ -183,8 +187,9 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a, c
                         int e0 = f.z - e1 - e2;
                         if ((e0 | e1 | e2) < 0) continue;
                         int4 g = d[2];
-                        float cx = (float)e1, cy = (float)e2, cz = (float)f.z;
-                        b0 = 1.0f - (cx + cy) / cz; b1 = cx / cz; b2 = cy / cz;
+                        // (cx+cy)/cz, cx/cz, cy/cz of scene.rs:189-193: integer operands, 0 <= numerator <= |cz| <= 2^21
+                        const float cx = (float)e1, cy = (float)e2, cz = (float)f.z, rcz = __int_as_float(g.w);
+                        b0 = 1.0f - exact_quotient(cx + cy, cz, rcz); b1 = exact_quotient(cx, cz, rcz); b2 = exact_quotient(cy, cz, rcz);
                         z = (b0 * __int_as_float(g.x) + b1 * __int_as_float(g.y)) + b2 * __int_as_float(g.z);
                     } else {
                         int4 g = d[2];
@@ -255,12 +260,14 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a, c
         // ---- (4) the tile's RGB, top-down rows, 16-byte stores when the frame layout allows ----
         const int rows = ty1 - ty0 + 1;
         if ((a.width & 15u) == 0u) {
-            const int vec_per_row = row_bytes >> 4;             // tile widths are multiples of 16 px here
-            for (int i = tid; i < rows * vec_per_row; i += kRasterThreads) {
-                int r = i / vec_per_row, c = i % vec_per_row;
-                uint4 v = touched ? *reinterpret_cast<const uint4*>(s_rgb + r * kRgbRow + c * 16) : make_uint4(0u, 0u, 0u, 0u);
-                uint8_t* dst = sa.rgb + ((size_t)(a.height - 1 - (ty0 + r)) * a.width + tx0) * 3;
-                reinterpret_cast<uint4*>(dst)[c] = v;
+            const int vec_per_row = row_bytes >> 4;             // tile widths are multiples of 16 px here; <= 12 vectors
+            const int c = tid & 15;
+            if (c < vec_per_row) {
+                for (int r = tid >> 4; r < rows; r += kRasterThreads / 16) {
+                    uint4 v = touched ? *reinterpret_cast<const uint4*>(s_rgb + r * kRgbRow + c * 16) : make_uint4(0u, 0u, 0u, 0u);
+                    uint8_t* dst = sa.rgb + ((size_t)(a.height - 1 - (ty0 + r)) * a.width + tx0) * 3;
+                    reinterpret_cast<uint4*>(dst)[c] = v;
+                }
             }
         } else {
             for (int i = tid; i < rows * row_bytes; i += kRasterThreads) {
