@@ -26,6 +26,10 @@
 
 namespace tr {
 
+#ifndef TR_PIXELS_PER_LANE
+#define TR_PIXELS_PER_LANE 2
+#endif
+
 // Kernel modes: a pipeline id (P_DEFAULT..P_OCCLUSION) = visibility + shading of that pipeline.
 constexpr int kModeDepthOnly = -2;     // K4: shadow buffer, `>=` max, no culling upstream
 constexpr int kModeVisibility = -1;    // K3 alone: keys only (camera pass of the many-light AO batch)
@@ -95,8 +99,12 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a, c
     const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
     const int tx1 = min(tx0 + kTileW, (int)a.width) - 1, ty1 = min(ty0 + kTileH, (int)a.height) - 1;
     const float kFloatMin = -3.402823466e38f;
+    constexpr int kPix = TR_PIXELS_PER_LANE;                // pixels per lane in the block loop (1 or 2)
+    constexpr int kBlockH = 4 * kPix;
     constexpr int kBlocksX = kTileW / 8;
-    constexpr int kBlocks = kBlocksX * (kTileH / 4);
+    constexpr int kBlocks = kBlocksX * (kTileH / kBlockH);
+    static_assert(kPix == 1 || kPix == 2, "the fragment stage selects between at most two pixels per lane");
+    static_assert(kTileH % kBlockH == 0, "tile height must hold whole blocks");
 
     const uint32_t tile = blockIdx.y * a.tiles_x + blockIdx.x;
     const uint32_t cell = (uint32_t)(ty0 / kCellH) * a.bins.cells_x + (uint32_t)(tx0 / kCellW);
@@ -145,7 +153,8 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a, c
         if (n_list == 0) break;             // (more is false here: a round that staged nothing reached the end)
         touched = true;
 
-        // ---- (2) warps pull 8x4 blocks off the tile; ballot the staged bboxes against the block, evaluate per pixel ----
+        // ---- (2) warps pull 8 x (4*kPix) blocks off the tile (a lane owns kPix pixels, 4 rows apart); ballot the staged
+        //      bboxes against the block, evaluate per pixel ----
 #ifdef TR_STATIC_BLOCKS
         for (int blk = warp; blk < kBlocks; blk += kRasterThreads / 32) {
 #else
@@ -155,84 +164,113 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a, c
             blk = __shfl_sync(0xffffffffu, blk, 0);
             if (blk >= kBlocks) break;
 #endif
-            const int bx0 = (blk % kBlocksX) * 8, by0 = (blk / kBlocksX) * 4;   // tile-relative
-            const int lx = bx0 + (lane & 7), ly = by0 + (lane >> 3);
+            const int bx0 = (blk % kBlocksX) * 8, by0 = (blk / kBlocksX) * kBlockH;   // tile-relative
+            const int lx = bx0 + (lane & 7), ly = by0 + (lane >> 3);                  // pixel k: (lx, ly + 4k)
             const int px = tx0 + lx, py = ty0 + ly;
-            const bool in = px < (int)a.width && py < (int)a.height;
-            // running winner: depth, low key word (epoch | polygon; kNoTri = nothing drawn yet) and its barycentrics
-            float bz = kFloatMin, w0 = 0.0f, w1 = 0.0f, w2 = 0.0f;
-            uint32_t blo = kNoTri;
-            if (from_memory && in) {
-                if (DEPTH_ONLY) bz = a.depth[(size_t)py * a.width + px];
-                else { unsigned long long k = a.keys[(size_t)py * a.width + px]; bz = key_depth(k); blo = key_lo(k); }
+            // running winners: depth, low key word (epoch | polygon; kNoTri = nothing drawn yet) and barycentrics
+            float bz[kPix], w0[kPix], w1[kPix], w2[kPix];
+            uint32_t blo[kPix];
+            bool in[kPix], fresh_winner[kPix];      // fresh: the winner was found in this round (w0..w2 are its barycentrics)
+#pragma unroll
+            for (int k = 0; k < kPix; ++k) {
+                in[k] = px < (int)a.width && py + 4 * k < (int)a.height;
+                bz[k] = kFloatMin; blo[k] = kNoTri; w0[k] = w1[k] = w2[k] = 0.0f; fresh_winner[k] = false;
+                if (from_memory && in[k]) {
+                    const size_t at = (size_t)(py + 4 * k) * a.width + px;
+                    if (DEPTH_ONLY) bz[k] = a.depth[at];
+                    else { unsigned long long key = a.keys[at]; bz[k] = key_depth(key); blo[k] = key_lo(key); }
+                }
             }
-            bool fresh_winner = false;      // the winner was found in this round (its barycentrics are in w0..w2)
             for (int base = 0; base < n_list; base += 32) {
                 int i = base + lane;
                 bool cand = false;
                 if (i < n_list) {
                     int lo = s_lo[i], hi = s_hi[i];
-                    cand = (lo >> 16) <= bx0 + 7 && (hi >> 16) >= bx0 && (lo & 0xffff) <= by0 + 3 && (hi & 0xffff) >= by0;
+                    cand = (lo >> 16) <= bx0 + 7 && (hi >> 16) >= bx0 && (lo & 0xffff) <= by0 + kBlockH - 1 && (hi & 0xffff) >= by0;
                 }
                 unsigned m = __ballot_sync(0xffffffffu, cand);
                 while (m) {
                     int j = base + __ffs(m) - 1;
                     m &= m - 1;
                     const int4* d = reinterpret_cast<const int4*>(s_tri + j * kStageWords);
-                    int4 e = d[0], f = d[1];
-                    float z, b0, b1, b2;
-                    if (!((uint32_t)f.w & kInexactFlag)) {
-                        int e1 = e.x + lx * e.y + ly * e.z;          // cx * sign(cz)
-                        int e2 = e.w + lx * f.x + ly * f.y;          // cy * sign(cz)
-                        int e0 = f.z - e1 - e2;
-                        if ((e0 | e1 | e2) < 0) continue;
-                        int4 g = d[2];
-                        // (cx+cy)/cz, cx/cz, cy/cz of scene.rs:189-193: integer operands, 0 <= numerator <= |cz| <= 2^21
-                        const float cx = (float)e1, cy = (float)e2, cz = (float)f.z, rcz = __int_as_float(g.w);
-                        b0 = 1.0f - exact_quotient(cx + cy, cz, rcz); b1 = exact_quotient(cx, cz, rcz); b2 = exact_quotient(cy, cz, rcz);
-                        z = (b0 * __int_as_float(g.x) + b1 * __int_as_float(g.y)) + b2 * __int_as_float(g.z);
-                    } else {
-                        int4 g = d[2];
-                        if (!fragment_depth(e.x, e.y, e.z, e.w, f.x, f.y, __int_as_float(g.x), __int_as_float(g.y), __int_as_float(g.z),
-                                            px, py, z, b0, b1, b2)) continue;
+                    const int4 e = d[0], f = d[1];
+                    const bool exact = !((uint32_t)f.w & kInexactFlag);
+                    int e1[kPix], e2[kPix];
+                    bool inside[kPix], any = !exact;
+                    if (exact) {
+                        e1[0] = e.x + lx * e.y + ly * e.z;           // cx * sign(cz)
+                        e2[0] = e.w + lx * f.x + ly * f.y;           // cy * sign(cz)
+#pragma unroll
+                        for (int k = 0; k < kPix; ++k) {
+                            if (k) { e1[k] = e1[k - 1] + 4 * e.z; e2[k] = e2[k - 1] + 4 * f.y; }
+                            inside[k] = ((f.z - e1[k] - e2[k]) | e1[k] | e2[k]) >= 0;
+                            any = any || inside[k];
+                        }
                     }
-                    if (z != z) { atomicAdd(&a.diag[D_NAN_DEPTH], 1ull); continue; }
-                    if (DEPTH_ONLY) {
-                        if (z >= bz) bz = z;                                     // shader.rs:703
-                    } else {
-                        // shader.rs:175 `z <= zbuf -> reject`, applied in polygon order == key_beats() on packed keys
-                        uint32_t lo = (a.epoch << 24) | ((uint32_t)f.w & kTriMask);
-                        if (z > bz || (z == bz && lo < blo && blo != kNoTri)) {
-                            bz = z; blo = lo;
-                            if (SHADE) { w0 = b0; w1 = b1; w2 = b2; fresh_winner = true; }
+                    if (!any) continue;
+                    const int4 g = d[2];
+                    const uint32_t lo = (a.epoch << 24) | ((uint32_t)f.w & kTriMask);
+#pragma unroll
+                    for (int k = 0; k < kPix; ++k) {
+                        float z, b0, b1, b2;
+                        if (exact) {
+                            if (!inside[k]) continue;
+                            // (cx+cy)/cz, cx/cz, cy/cz of scene.rs:189-193: integer operands, 0 <= numerator <= |cz| <= 2^21
+                            const float cx = (float)e1[k], cy = (float)e2[k], cz = (float)f.z, rcz = __int_as_float(g.w);
+                            b0 = 1.0f - exact_quotient(cx + cy, cz, rcz); b1 = exact_quotient(cx, cz, rcz); b2 = exact_quotient(cy, cz, rcz);
+                            z = (b0 * __int_as_float(g.x) + b1 * __int_as_float(g.y)) + b2 * __int_as_float(g.z);
+                        } else {
+                            if (!fragment_depth(e.x, e.y, e.z, e.w, f.x, f.y, __int_as_float(g.x), __int_as_float(g.y), __int_as_float(g.z),
+                                                px, py + 4 * k, z, b0, b1, b2)) continue;
+                        }
+                        if (z != z) { atomicAdd(&a.diag[D_NAN_DEPTH], 1ull); continue; }
+                        if (DEPTH_ONLY) {
+                            if (z >= bz[k]) bz[k] = z;                               // shader.rs:703
+                        } else if (z > bz[k] || (z == bz[k] && lo < blo[k] && blo[k] != kNoTri)) {
+                            // shader.rs:175 `z <= zbuf -> reject`, applied in polygon order == key_beats() on packed keys
+                            bz[k] = z; blo[k] = lo;
+                            if (SHADE) { w0[k] = b0; w1[k] = b1; w2[k] = b2; fresh_winner[k] = true; }
                         }
                     }
                 }
             }
-            if (in) {
-                if (DEPTH_ONLY) a.depth[(size_t)py * a.width + px] = bz;
-                else a.keys[(size_t)py * a.width + px] = make_key(bz, blo);
+#pragma unroll
+            for (int k = 0; k < kPix; ++k) {
+                if (!in[k]) continue;
+                const size_t at = (size_t)(py + 4 * k) * a.width + px;
+                if (DEPTH_ONLY) a.depth[at] = bz[k];
+                else a.keys[at] = make_key(bz[k], blo[k]);
             }
             if (SHADE && !more) {
-                // ---- (3) fragment stage for the winner, if it passed the depth test in THIS render ----
-                uint32_t out = 0u;
-                const bool shaded = in && blo != kNoTri && (blo >> 24) == a.epoch;
-                if (shaded) {
-                    if (!fresh_winner) {        // won in an earlier round of a long list: re-derive its barycentrics
-                        const float4* r = a.rec + (size_t)(blo & kTriMask) * 4;
-                        float4 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
-                        float zz;
-                        fragment_depth(__float_as_int(r0.x), __float_as_int(r0.y), __float_as_int(r0.z), __float_as_int(r0.w),
-                                       __float_as_int(r1.x), __float_as_int(r1.y), r1.z, r1.w, r2.x, px, py, zz, w0, w1, w2);
+                // ---- (3) fragment stage for the winners that passed the depth test in THIS render; one copy of the
+                //      fragment code (the pixel's state is selected into scalars) keeps the kernel in the instruction cache
+#pragma unroll 1
+                for (int k = 0; k < kPix; ++k) {
+                    const bool second = k != 0;
+                    float z = bz[0], v0 = w0[0], v1 = w1[0], v2 = w2[0];
+                    uint32_t lo = blo[0];
+                    bool pin = in[0], fresh = fresh_winner[0];
+                    if (kPix > 1 && second) { z = bz[kPix - 1]; v0 = w0[kPix - 1]; v1 = w1[kPix - 1]; v2 = w2[kPix - 1]; lo = blo[kPix - 1]; pin = in[kPix - 1]; fresh = fresh_winner[kPix - 1]; }
+                    const int qy = py + 4 * k, sy = ly + 4 * k;
+                    uint32_t out = 0u;
+                    const bool shaded = pin && lo != kNoTri && (lo >> 24) == a.epoch;
+                    if (shaded) {
+                        if (!fresh) {           // won in an earlier round of a long list: re-derive its barycentrics
+                            const float4* r = a.rec + (size_t)(lo & kTriMask) * 4;
+                            float4 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
+                            float zz;
+                            fragment_depth(__float_as_int(r0.x), __float_as_int(r0.y), __float_as_int(r0.z), __float_as_int(r0.w),
+                                           __float_as_int(r1.x), __float_as_int(r1.y), r1.z, r1.w, r2.x, px, qy, zz, v0, v1, v2);
+                        }
+                        out = shade_pixel<SHADE ? MODE : 0>(sa, u, lo & kTriMask, px, qy, z, v0, v1, v2);
                     }
-                    out = shade_pixel<SHADE ? MODE : 0>(sa, u, blo & kTriMask, px, py, bz, w0, w1, w2);
-                }
-                if (rgb_bulk) {
-                    uint8_t* p = s_rgb + ly * kRgbRow + lx * 3;
-                    p[0] = (uint8_t)out; p[1] = (uint8_t)(out >> 8); p[2] = (uint8_t)(out >> 16);
-                } else if (shaded) {
-                    uint8_t* p = sa.rgb + ((size_t)(a.height - 1 - py) * a.width + px) * 3;
-                    p[0] = (uint8_t)out; p[1] = (uint8_t)(out >> 8); p[2] = (uint8_t)(out >> 16);
+                    if (rgb_bulk) {
+                        uint8_t* p = s_rgb + sy * kRgbRow + lx * 3;
+                        p[0] = (uint8_t)out; p[1] = (uint8_t)(out >> 8); p[2] = (uint8_t)(out >> 16);
+                    } else if (shaded) {
+                        uint8_t* p = sa.rgb + ((size_t)(a.height - 1 - qy) * a.width + px) * 3;
+                        p[0] = (uint8_t)out; p[1] = (uint8_t)(out >> 8); p[2] = (uint8_t)(out >> 16);
+                    }
                 }
             }
         }
