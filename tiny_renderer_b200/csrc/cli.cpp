@@ -19,7 +19,8 @@ static int die(const char* what) {
 }
 
 int main(int argc, char** argv) {
-    std::string asset_path = "assets/diablo", pipeline = "default", out = "out.tga", dump_z, dump_shadow;
+    std::string asset_path = "assets/diablo", pipeline = "default", out = "out.tga", dump_z, dump_shadow, replay;
+    float fixed_dt = -1.0f;
     uint32_t width = 800, height = 800, frames = 1;
     float camera_angle = 0.0f, light_angle = 0.0f, camera_step = 0.0f;
     int device = 0;
@@ -42,11 +43,15 @@ int main(int argc, char** argv) {
         else if (a == "--device") device = atoi(next("--device"));
         else if (a == "--dump-z") dump_z = next("--dump-z");
         else if (a == "--dump-shadow") dump_shadow = next("--dump-shadow");
+        else if (a == "--replay") replay = next("--replay");
+        else if (a == "--dt") fixed_dt = strtof(next("--dt"), nullptr);
         else if (a == "--quiet") print_fps = false;
         else if (a == "--help" || a == "-h") {
             printf("usage: tiny_renderer [-p asset_dir] [-s default|phong|normal_map|true_normal|specular|darboux|shadow|occlusion]\n"
                    "       [--out file.tga] [--width W] [--height H] [--camera-angle rad] [--light-angle rad]\n"
-                   "       [--frames N --camera-step rad] [--dump-z file.tga] [--dump-shadow file.tga] [--device N] [--quiet]\n");
+                   "       [--frames N --camera-step rad] [--dump-z file.tga] [--dump-shadow file.tga] [--device N] [--quiet]\n"
+                   "       [--replay keys.txt [--dt seconds]]   one line per frame: keys pressed during that frame (a d = camera,\n"
+                   "                                            q e = light, x = Escape released); the app loop of the reference, headless\n");
             return 0;
         }
         // unknown arguments are ignored, like the reference (main.rs:24)
@@ -58,6 +63,56 @@ int main(int argc, char** argv) {
     std::vector<uint8_t> frame((size_t)width * height * 3);
     const float at[3] = {0, 0, 0}, up[3] = {0, 1, 0};
     auto t0 = std::chrono::steady_clock::now();
+    if (!replay.empty()) {
+        // Scripted interaction replay: the reference's app loop (app.rs:166-247) with the window's key events read from a
+        // file.  Angles integrate SPEED * previous frame time (app.rs:173-199, CAMERA_SPEED = LIGHT_SOURCE_SPEED = 3.0,
+        // app.rs:12-13); keys a/d move the camera, q/e the light, Escape (x) ends the loop at the start of the next frame
+        // (app.rs:63-77, 224-227).  --dt fixes the frame time (deterministic replays); otherwise it is measured.
+        FILE* fp = fopen(replay.c_str(), "r");
+        if (!fp) { fprintf(stderr, "tiny_renderer: cannot open %s\n", replay.c_str()); return 1; }
+        const float kCameraSpeed = 3.0f, kLightSpeed = 3.0f;
+        bool cam_l = false, cam_r = false, light_l = false, light_r = false, exit_app = false;
+        float frame_time = 0.0f;
+        uint32_t shown = 0, fps_counter = 0;
+        auto fps_begin = std::chrono::steady_clock::now();
+        char line[256];
+        while (!exit_app) {
+            auto frame_begin = std::chrono::steady_clock::now();
+            if (tr_scene_clear(scene)) return die("clear");
+            if (cam_r) camera_angle += kCameraSpeed * frame_time;
+            if (cam_l) camera_angle -= kCameraSpeed * frame_time;
+            if (light_r) light_angle += kLightSpeed * frame_time;
+            if (light_l) light_angle -= kLightSpeed * frame_time;
+            const float from[3] = {sinf(camera_angle), 0.0f, cosf(camera_angle)};
+            const float light[3] = {sinf(light_angle), 0.0f, cosf(light_angle)};
+            if (tr_scene_set_light_direction(scene, light)) return die("set_light_direction");
+            if (tr_scene_set_camera(scene, from, at, up)) return die("set_camera");
+            if (tr_scene_render(scene)) return die("render");
+            if (tr_scene_get_frame_buffer(scene, frame.data())) return die("get_frame_buffer");   // window.set_image in the reference
+            ++shown;
+            cam_l = cam_r = light_l = light_r = false;                                             // frame_action_buffer.reset()
+            if (!fgets(line, sizeof line, fp)) exit_app = true;                                    // end of script = window closed
+            else for (const char* c = line; *c; ++c) {
+                if (*c == 'a') cam_l = true; else if (*c == 'd') cam_r = true;
+                else if (*c == 'q') light_l = true; else if (*c == 'e') light_r = true;
+                else if (*c == 'x') exit_app = true;
+            }
+            if (print_fps) {
+                ++fps_counter;
+                if (std::chrono::duration<float>(std::chrono::steady_clock::now() - fps_begin).count() > 1.0f) {
+                    printf("FPS --- %u\n", fps_counter);                                          // app.rs:238
+                    fps_begin = std::chrono::steady_clock::now();
+                    fps_counter = 0;
+                }
+            }
+            frame_time = fixed_dt >= 0.0f ? fixed_dt : std::chrono::duration<float>(std::chrono::steady_clock::now() - frame_begin).count();
+        }
+        fclose(fp);
+        double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        printf("replayed %u frames in %.3f s (%.1f frames/s), camera angle %.9g, light angle %.9g\n", shown, secs, shown / secs,
+               (double)camera_angle, (double)light_angle);
+        frames = 0;
+    }
     for (uint32_t f = 0; f < frames; ++f) {
         float ca = camera_angle + camera_step * (float)f;
         const float from[3] = {sinf(ca), 0.0f, cosf(ca)};
