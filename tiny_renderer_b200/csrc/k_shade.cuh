@@ -41,7 +41,10 @@ __device__ __forceinline__ uchar4 fetch_texel(const Maps& mp, int which, int siz
 }
 // util.rs:51-56 / 67-72
 __device__ __forceinline__ f3 decode_normal(uchar4 c) {
-    return unit3(f3{(float)c.x / 255.0f - 0.5f, (float)c.y / 255.0f - 0.5f, (float)c.z / 255.0f - 0.5f});
+    // c / 255.0 with integer c in 0..255: exact_quotient gives the IEEE quotient (integer operands far below 2^21)
+    const float r255 = 1.0f / 255.0f;
+    return unit3(f3{exact_quotient((float)c.x, 255.0f, r255) - 0.5f, exact_quotient((float)c.y, 255.0f, r255) - 0.5f,
+                    exact_quotient((float)c.z, 255.0f, r255) - 0.5f});
 }
 // color_blend(c, (0,0,0), t), util.rs:7-13
 __device__ __forceinline__ uint32_t blend_black(uint32_t c, float t) { return cast_u8(t * (float)c + (1.0f - t) * 0.0f); }
