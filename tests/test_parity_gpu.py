@@ -140,3 +140,26 @@ def test_exact_quotient_selftest(tinyr):
     for seed in (1, 0xDEADBEEF):
         rc = tinyr.lib().tr_selftest_exact_quotient(0, 1 << 30, seed, ctypes.byref(bad))
         assert rc == 0 and bad.value == 0, (rc, bad.value)
+
+
+@pytest.mark.parametrize("pipeline", PIPELINES)
+@pytest.mark.parametrize("asset", ["african_head", "diablo"])
+def test_turntable_sweep_8_angles(tinyr, oracle, asset, pipeline):
+    """SURVEY.md §4 test plan: every pipeline x both assets x 8 camera angles (2*pi*k/8) with a moving light, one
+    scene object reused across the views like the app loop does (clear between frames)."""
+    from tiny_renderer_b200.scene import Scene
+    model = get_model(asset)
+    w, h = 416, 400
+    g = Scene(w, h, model, pipeline)
+    o = oracle.OracleScene(w, h, model, pipeline)
+    for k in range(8):
+        lf, la, up, light = assets.view_vectors(2 * math.pi * k / 8, 0.7 + 0.35 * k)
+        if pipeline in TWO_PASS and abs(math.cos(0.7 + 0.35 * k)) > 0.98 and math.cos(0.7 + 0.35 * k) < 0:
+            continue                                    # light ~ -z: rotation_between is (nearly) undefined, shader.rs:921
+        parity.drive(g, lf, la, up, light)
+        parity.drive(o, lf, la, up, light)
+        st = parity.compare(g, o, two_pass=pipeline in TWO_PASS)
+        if pipeline != "specular":
+            assert st["rgb_exact_frac"] == 1.0, (k, st)
+        assert st["depth_bits_differ"] == 0, (k, st)
+    g.close()

@@ -2,7 +2,7 @@
 //
 // One CTA owns one kTileW x kTileH screen tile.  (1) It filters the polygon list of the binning cell the tile lies
 // in (K1+K2; a scan of all bounding boxes when the cell's bin overflowed) against the tile and stages per-polygon
-// edge equations in shared memory.  (2) Warps pull 8x4-pixel blocks off the tile, one pixel per lane: 32 lanes test
+// edge equations in shared memory.  (2) Warps pull 8x8-pixel blocks off the tile, two pixels per lane: 32 lanes test
 // 32 staged bounding boxes against the block, a ballot yields the candidate mask, and every lane evaluates the
 // inside test for its own pixel with operands broadcast from shared memory.  Visibility is resolved in registers —
 // (depth, epoch|polygon) compared the way a 64-bit atomicMin on the packed key would order them, without the L2
@@ -15,8 +15,8 @@
 // (/root/reference/src/scene.rs:174-197), rejects bar.* < 0 (:245) and takes z = bar . z (shader.rs:174).  When
 // the polygon's unclamped bounding box is at most kExactExtent pixels wide and high every product and sum in c
 // is an integer below 2^24, hence exact in f32, and `bar.* >= 0` is equivalent to the integer edge tests used
-// here (proof in DESIGN.md §K3); the divisions and z are then done in f32 exactly as the reference does, for
-// inside pixels only.  Larger polygons take the literal f32 path (fragment_depth).
+// here (proof in DESIGN.md §4); the three quotients are formed by exact_quotient() (k_tile.cuh: bit-identical to the
+// IEEE division for these integer operands) and z in f32 exactly as the reference does, for inside pixels only.  Larger polygons take the literal f32 path (fragment_depth).
 //
 // Replaces scene.rs:232-258 and process_z_value (/root/reference/src/scene/shader.rs:169-180) plus the fragment
 // closures (k_shade.cuh); in depth-only mode the pass-1 fragment shaders of shadow / occlusion
@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a, c
     __shared__ int s_warp_count[kRasterThreads / 32];
     __shared__ int s_count;
     __shared__ int s_next;
-    __shared__ int s_block;                                 // next 8x4 block of the tile to hand to a warp
+    __shared__ int s_block;                                 // next block of the tile to hand to a warp
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
