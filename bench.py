@@ -152,9 +152,9 @@ def run_reference(args, rank, world):
     model, data = bench_model()
     cores = os.cpu_count() or 1
     views = view_batch()
-    # One reference step = a bounded sample of the GPU arm's step (16 frames): 2 of the 8 views of each pipeline, so
+    # One reference step = a bounded sample of the GPU arm's step (16 frames): 2..8 of the 8 views of each pipeline, so
     # that any --steps K the driver passes ends within minutes (a 4K frame costs ~0.15-0.5 s of one host core).
-    sample_views = 2
+    sample_views = max(2, min(N_ANGLES, cores // len(PIPES)))      # enough frames to occupy every host thread
     jobs = [(p, views[k]) for p in PIPES for k in range(sample_views)]
     threads = min(cores, len(jobs))
     times = []
@@ -196,6 +196,20 @@ def algorithmic_bytes(n_px, covered, n_tri, pipe):
     k1 = n_tri * (96 + 64 + 16 + (96 if pipe == "darboux" else 16))
     k35 = 19 * n_px + tex + n_tri * (64 + 16 + 96)
     return {"K1_vertex_setup": k1, "K3_raster_visibility": k35, "frame": 19 * n_px + tex + k1}
+
+
+def ncu_traffic(pipe):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused tile kernel, from the committed
+    `ncu --set full` capture (profiles/r1d_traffic.json); None when the file is absent."""
+    p = os.path.join(ROOT, "profiles", "r1d_traffic.json")
+    if not os.path.exists(p):
+        return None
+    want = "k_raster<%d>" % {"phong": 1, "darboux": 4}[pipe]
+    with open(p) as f:
+        for k, v in json.load(f).items():
+            if want in k:
+                return v["dram_bytes_per_launch"]
+    return None
 
 
 def batch_roofline(us_per_frame, n_px, covered, n_tri, peak):
@@ -380,7 +394,7 @@ def run_gpu(args, rank, world, local_rank):
         us, p, k, nbytes, frame_bytes, frame_us = best
         achieved = nbytes / (us * 1e-6) / 1e9
         line["roofline"] = {"bound": "hbm", "kernel": "k_raster<%s> = K3 raster_visibility + K5 shade fused" % p, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                            "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                            "frac": achieved / peak, "traffic": ncu_traffic(p), "peak_source": peak_src,
                             "algorithmic_bytes_per_launch": nbytes, "us_per_launch": us,
                             "note": "kernel timed one frame at a time (CUDA events on the launching stream, profiling mode); "
                                     "`batch` is the same byte count over the overlapped view batch of the timed region",
