@@ -173,3 +173,26 @@ def test_config5_8k_properties(tinyr):
     cs2 = g.render_views(views[2:3], want_checksums=True)
     assert int(cs2[0]) == int(cs[2])
     g.close()
+
+
+@pytest.mark.parametrize("asset", ["african_head", "diablo"])
+def test_config5_8k_full_pixel_parity_sample(tinyr, oracle, asset):
+    """BASELINE config 5: specular at 7680x4320, a fixed sample of the 2048-view turntable (k = 0, 768, 1536 here;
+    the oracle needs ~1 s per 8K view) rendered as one overlapped batch, every pixel against the oracle."""
+    from tiny_renderer_b200.scene import Scene
+    m = get_model(asset)
+    w, h = 7680, 4320
+    ks = [0, 768, 1536]
+    views = turntable(2048)[ks]
+    g = Scene(w, h, m, "specular", ring=3)
+    frames = np.zeros((len(ks), h, w, 3), np.uint8)
+    g.render_views(views, want_checksums=False, frames_out=frames)
+    vis_last = g.raw_visibility()
+    o = oracle.OracleScene(w, h, m, "specular")
+    for i, k in enumerate(ks):
+        parity.drive(o, views[i, 0:3], views[i, 3:6], views[i, 6:9], views[i, 9:12])
+        d = np.abs(frames[i].astype(np.int16) - o.get_frame_buffer().astype(np.int16)).max(axis=2)
+        assert d.max() <= 1 and (d == 0).mean() >= 0.999, (k, int(d.max()), float((d == 0).mean()))
+    assert np.array_equal(vis_last, o.raw_visibility())          # visibility of the last view, bit-exact
+    assert o.diagnostics()["texel_oob"] == 0
+    g.close()
