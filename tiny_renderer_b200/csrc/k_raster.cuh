@@ -48,6 +48,7 @@ struct RasterArgs {
     // is stale.  Scene::clear therefore costs nothing for tiles no polygon touches; K6 and the getters never read
     // their keys.
     uint32_t* tile_state;
+    const uint32_t* tile_order;   // launch position -> tile index (null = identity)
     float* depth;              // depth-only mode (shadow buffer)
     unsigned long long* diag;
 };
@@ -96,7 +97,10 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a, c
     __shared__ int s_block;                                 // next block of the tile to hand to a warp
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
+    // CTAs are handed out in launch order; tile_order lists the tiles from the screen centre outwards so that the
+    // tiles that usually carry the geometry start first and the cheap border tiles fill the tail of the grid.
+    const uint32_t tile = a.tile_order ? __ldg(&a.tile_order[blockIdx.x]) : blockIdx.x;
+    const int tx0 = (int)(tile % a.tiles_x) * kTileW, ty0 = (int)(tile / a.tiles_x) * kTileH;
     const int tx1 = min(tx0 + kTileW, (int)a.width) - 1, ty1 = min(ty0 + kTileH, (int)a.height) - 1;
     const float kFloatMin = -3.402823466e38f;
     constexpr int kPix = TR_PIXELS_PER_LANE;                // pixels per lane in the block loop (1 or 2)
@@ -106,7 +110,6 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a, c
     static_assert(kPix == 1 || kPix == 2, "the fragment stage selects between at most two pixels per lane");
     static_assert(kTileH % kBlockH == 0, "tile height must hold whole blocks");
 
-    const uint32_t tile = blockIdx.y * a.tiles_x + blockIdx.x;
     const uint32_t cell = (uint32_t)(ty0 / kCellH) * a.bins.cells_x + (uint32_t)(tx0 / kCellW);
     const uint32_t n_bin = a.bins.count[a.bins.parity * a.bins.n_cells + cell];
     const bool cleared = a.fresh || (!DEPTH_ONLY && a.tile_state[tile] != 0u);

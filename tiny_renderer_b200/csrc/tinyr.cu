@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <algorithm>
 #include <vector>
 
 using namespace tr;
@@ -54,6 +55,8 @@ struct tr_scene {
     };
     std::vector<Slot> slots;
     uint32_t tiles_x = 0, tiles_y = 0;
+    uint32_t* tile_order = nullptr;      // tiles sorted by distance from the screen centre (launch order of K3/K4)
+    bool overlapping = false;            // a batch is running frames / light passes concurrently on the slot streams
     uint32_t* ao = nullptr;
     AoList ao_list{};                  // covered pixels of the camera view (many-light AO batch), allocated on first use
     uint32_t ao_list_n = 0;
@@ -231,6 +234,19 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
     s->tiles_x = (s->width + kTileW - 1) / kTileW;
     s->tiles_y = (s->height + kTileH - 1) / kTileH;
     const size_t n_tiles = (size_t)s->tiles_x * s->tiles_y;
+    {
+        std::vector<uint32_t> order(n_tiles);
+        for (size_t i = 0; i < n_tiles; ++i) order[i] = (uint32_t)i;
+        const double cx = 0.5 * (s->tiles_x - 1), cy = 0.5 * (s->tiles_y - 1);
+        // distance in pixels (tiles are kTileW x kTileH), ties by index: a deterministic order
+        auto dist = [&](uint32_t t) {
+            double dx = ((double)(t % s->tiles_x) - cx) * kTileW, dy = ((double)(t / s->tiles_x) - cy) * kTileH;
+            return dx * dx + dy * dy;
+        };
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t p, uint32_t q) { return dist(p) < dist(q); });
+        CU(cudaMalloc(&s->tile_order, n_tiles * 4));
+        CU(cudaMemcpy(s->tile_order, order.data(), n_tiles * 4, cudaMemcpyHostToDevice));
+    }
     s->slots.assign(s->ring, tr_scene::Slot{});
     for (uint32_t r = 0; r < s->ring; ++r) {
         tr_scene::Slot& sl = s->slots[r];
@@ -285,7 +301,7 @@ void destroy_impl(tr_scene* s) {
         cudaFree(sl.cam.rec); cudaFree(sl.cam.var); cudaFree(sl.cam.bbox); cudaFree(sl.lit.rec); cudaFree(sl.lit.bbox);
         cudaFree(sl.bins.count); cudaFree(sl.bins.list);
     }
-    cudaFree(s->geom); cudaFree(s->ao); cudaFree(s->ao_list.frag); cudaFree(s->ao_list.pix); cudaFree(s->ao_list.count); cudaFree(s->diag); cudaFree(s->d_checksums); cudaFree(s->scratch);
+    cudaFree(s->geom); cudaFree(s->tile_order); cudaFree(s->ao); cudaFree(s->ao_list.frag); cudaFree(s->ao_list.pix); cudaFree(s->ao_list.count); cudaFree(s->diag); cudaFree(s->d_checksums); cudaFree(s->scratch);
     if (s->own_stream) cudaStreamDestroy(s->own_stream);
     delete s;
 }
@@ -323,7 +339,10 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     a.epoch = epoch; a.fresh = fresh ? 1 : 0;
     a.keys = S(s).keys; a.tile_state = S(s).tile_state; a.depth = S(s).shadow; a.diag = s->diag;
     ShadeArgs sa = shade_args(s, fresh_rgb);
-    dim3 grid(s->tiles_x, s->tiles_y);
+    // centre-out launch order shortens a lone frame's tail; overlapped batches do better in plain row order, where one
+    // frame's cheap border tiles run beside the previous frame's heavy ones (measured: profiles/README.md)
+    a.tile_order = s->overlapping ? nullptr : s->tile_order;
+    dim3 grid(s->tiles_x * s->tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
 #define TR_RASTER(M) k_raster<M><<<grid, kRasterThreads, 0, s->stream>>>(a, sa, u)
     switch (mode) {
