@@ -32,7 +32,7 @@ METRIC = "Mpixels/s shaded (device-timed) at 3840x2160"
 PIPES = ("phong", "darboux")
 N_ANGLES = 8
 LIGHT_ANGLE = 0.7
-RING = 4   # 4 x (8 B keys + 3 B rgb) x 8.29 Mpx = 365 MB of render targets > 126 MB L2
+RING = int(os.environ.get("TINYR_RING", "4"))   # 4 x (8 B keys + 3 B rgb) x 8.29 Mpx = 365 MB of render targets > 126 MB L2
 
 
 def load_peaks():

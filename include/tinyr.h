@@ -134,6 +134,9 @@ int tr_scene_kernel_times(tr_scene* s, float total_ms[8], uint64_t launches[8]);
 /* Device self-test of the rasteriser's 3-instruction exact division (k_tile.cuh exact_quotient) against IEEE f32
  * division over n_pairs pseudo-random integer pairs 0 <= a <= b <= 2^21; *mismatches must come back 0. */
 int tr_selftest_exact_quotient(int device, uint64_t n_pairs, uint64_t seed, uint64_t* mismatches);
+/* Device self-test of the fragment stage's shared-divisor quotients (k_tile.cuh shared_divisor/quotient: nvcc's own
+ * division sequence with the divisor-only part hoisted) against `a / b`; *mismatches must come back 0. */
+int tr_selftest_shared_divisor(int device, uint64_t n_pairs, uint64_t seed, uint64_t* mismatches);
 void* tr_host_alloc(size_t bytes);                                                /* pinned host memory for fast get_* copies */
 void tr_host_free(void* p);
 

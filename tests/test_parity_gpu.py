@@ -163,3 +163,13 @@ def test_turntable_sweep_8_angles(tinyr, oracle, asset, pipeline):
             assert st["rgb_exact_frac"] == 1.0, (k, st)
         assert st["depth_bits_differ"] == 0, (k, st)
     g.close()
+
+
+def test_shared_divisor_selftest(tinyr):
+    """Several quotients with one divisor (normalisations, 3x3 inverse, homogeneous divides of the fragment stage):
+    nvcc's own division sequence with the divisor-only instructions hoisted, against `a / b` on 2^31 pairs."""
+    import ctypes
+    bad = ctypes.c_uint64(123)
+    for seed in (7, 0xC0FFEE):
+        rc = tinyr.lib().tr_selftest_shared_divisor(0, 1 << 30, seed, ctypes.byref(bad))
+        assert rc == 0 and bad.value == 0, (rc, bad.value)

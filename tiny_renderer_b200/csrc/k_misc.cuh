@@ -81,6 +81,35 @@ __global__ void __launch_bounds__(256) k_selftest_quotient(unsigned long long n,
     if (bad) atomicAdd(mismatches, bad);
 }
 
+// Self-test of shared_divisor()/quotient() (k_tile.cuh) against `a / b`: divisors of moderate magnitude, numerators
+// from vanishing to 2^12 times the divisor (what normalisations and homogeneous divides feed it).  Counts results whose
+// bits differ from the division's, ignoring the sign of a zero result.
+__global__ void __launch_bounds__(256) k_selftest_shared_divisor(unsigned long long n, unsigned long long seed, unsigned long long* mismatches) {
+    unsigned long long i0 = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x, stride = (unsigned long long)gridDim.x * blockDim.x;
+    unsigned long long bad = 0;
+    for (unsigned long long i = i0; i < n; i += stride) {
+        unsigned long long z = seed + (i + 1ull) * 0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        // b: random mantissa, exponent in [-24, 24], random sign
+        uint32_t eb = 127u - 24u + (uint32_t)((z >> 23) % 49ull);
+        float b = __uint_as_float((uint32_t)(z & 0x7FFFFFu) | (eb << 23) | ((uint32_t)(z >> 63) << 31));
+        // a: random mantissa, exponent = exponent(b) + [-40, 12]
+        unsigned long long w = z * 0xD6E8FEB86659FD93ull + 0x2545F4914F6CDD1Dull;
+        w ^= w >> 32;
+        uint32_t ea = eb - 40u + (uint32_t)((w >> 23) % 53ull);
+        float a = __uint_as_float((uint32_t)(w & 0x7FFFFFu) | (ea << 23) | ((uint32_t)(w >> 63) << 31));
+        if ((i & 31ull) == 0ull) a = b;                                   // quotient exactly 1
+        if ((i & 31ull) == 1ull) a = 0.0f;
+        float q_ref = a / b;
+        float q = in_fast_division_range(b) ? quotient(a, shared_divisor(b)) : a / b;
+        bool same = __float_as_uint(q) == __float_as_uint(q_ref) || (q == 0.0f && q_ref == 0.0f);
+        bad += same ? 0ull : 1ull;
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
+
 // K8: position-weighted 64-bit checksum of a byte image viewed as little-endian u32 words:
 // sum_i word_i * (2 i + 1) mod 2^64 (tr_checksum_rgb8 is the host twin).  n_words = bytes / 4 (bytes % 4 == 0).
 __global__ void __launch_bounds__(256) k_checksum(const uint32_t* words, size_t n_words, unsigned long long* out) {

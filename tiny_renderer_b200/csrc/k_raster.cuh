@@ -26,6 +26,13 @@
 
 namespace tr {
 
+#ifdef TR_MIN_CTAS
+#define TR_RASTER_BOUNDS __launch_bounds__(kRasterThreads, TR_MIN_CTAS)
+#else
+// the compiler's own register choice measured best, except for the darboux instantiation, which lands at 65
+// registers (3 CTAs per SM) unless held to 4 CTAs per SM (A/B in profiles/README.md)
+#define TR_RASTER_BOUNDS __launch_bounds__(kRasterThreads, MODE == P_DARBOUX ? 4 : 0)
+#endif
 #ifndef TR_PIXELS_PER_LANE
 #define TR_PIXELS_PER_LANE 2
 #endif
@@ -84,7 +91,7 @@ __device__ __forceinline__ void stage_polygon(const RasterArgs& a, uint32_t t, i
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(kRasterThreads) k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u) {
+__global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u) {
     constexpr bool DEPTH_ONLY = MODE == kModeDepthOnly;
     constexpr bool SHADE = MODE >= 0;
     constexpr int kRgbRow = kTileW * 3;

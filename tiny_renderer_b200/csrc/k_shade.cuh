@@ -43,7 +43,7 @@ __device__ __forceinline__ uchar4 fetch_texel(const Maps& mp, int which, int siz
 __device__ __forceinline__ f3 decode_normal(uchar4 c) {
     // c / 255.0 with integer c in 0..255: exact_quotient gives the IEEE quotient (integer operands far below 2^21)
     const float r255 = 1.0f / 255.0f;
-    return unit3(f3{exact_quotient((float)c.x, 255.0f, r255) - 0.5f, exact_quotient((float)c.y, 255.0f, r255) - 0.5f,
+    return unit3_shared(f3{exact_quotient((float)c.x, 255.0f, r255) - 0.5f, exact_quotient((float)c.y, 255.0f, r255) - 0.5f,
                     exact_quotient((float)c.z, 255.0f, r255) - 0.5f});
 }
 // color_blend(c, (0,0,0), t), util.rs:7-13
@@ -85,14 +85,14 @@ __device__ __forceinline__ float shadow_lookup(const float* shadow, f3 s, uint32
 __device__ __forceinline__ uint32_t occlusion_gray(const float* shadow, const Uniforms& u, int px, int py, float z, f3 wp, DiagLocal& dl) {
     const uint32_t n_px = u.width * u.height;
     bool ok;
-    f3 fs = dehomog(xform(u.shadow_from_screen, f4{(float)px, (float)py, z, 1.0f}), ok);
+    f3 fs = dehomog_shared(xform(u.shadow_from_screen, f4{(float)px, (float)py, z, 1.0f}), ok);
     dl.w_zero += ok ? 0u : 1u;
     float fsv = shadow_lookup(shadow, fs, u.width, n_px, dl);
     float occ = 1.0f;
 #pragma unroll 4
     for (int k = 0; k < 16; ++k) {
         f3 sp = wp + u.ao_step[k];
-        f3 sc = dehomog(xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f}), ok);
+        f3 sc = dehomog_shared(xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f}), ok);
         dl.w_zero += ok ? 0u : 1u;
         float sv = shadow_lookup(shadow, sc, u.width, n_px, dl);
         if (sv - 1.0f > fsv) {
@@ -135,7 +135,7 @@ __device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Unifor
         if (PIPE == P_SHADOW) {
             bool ok;
             DiagLocal dl;
-            f3 s = dehomog(xform(u.shadow_from_screen, f4{(float)px, (float)py, z, 1.0f}), ok);
+            f3 s = dehomog_shared(xform(u.shadow_from_screen, f4{(float)px, (float)py, z, 1.0f}), ok);
             dl.w_zero += ok ? 0u : 1u;
             float sv = shadow_lookup(a.shadow, s, u.width, u.width * u.height, dl);
             dl.flush(a.diag);
@@ -145,10 +145,10 @@ __device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Unifor
     } else if (PIPE == P_NORMAL_MAP || PIPE == P_SPECULAR) {
         f3 nm = decode_normal(fetch_texel(a.maps, 1, 1, uv, a.diag));
         f4 t = xform(u.it_m, f4{nm.x, nm.y, nm.z, 0.0f});
-        f3 n = unit3(f3{t.x, t.y, t.z});                                          // shader.rs:451-454
+        f3 n = unit3_shared(f3{t.x, t.y, t.z});                                        // shader.rs:451-454
         diff = dot3(u.t_light, n);
         if (PIPE == P_SPECULAR) {
-            f3 refl = unit3((n * dot3(u.t_light, n)) * 2.0f - u.t_light);         // shader.rs:515-518
+            f3 refl = unit3_shared((n * dot3(u.t_light, n)) * 2.0f - u.t_light);         // shader.rs:515-518
             float e = (float)fetch_texel(a.maps, 3, 3, uv, a.diag).x;              // util.rs:82: raw 0..255
             float spec = 0.6f * powf(fmaxf(refl.z, 0.0f), e);
             float k = diff + spec;
@@ -160,21 +160,29 @@ __device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Unifor
         float4 v0 = __ldg(&v[0]), v1 = __ldg(&v[1]), v2 = __ldg(&v[2]), v3 = __ldg(&v[3]), v4 = __ldg(&v[4]), v5 = __ldg(&v[5]);
         mat3 N = {{v3.x, v3.w, v4.z, v3.y, v4.x, v4.w, v3.z, v4.y, v5.x}};         // vertex_t_normals, columns n0 n1 n2
         f3 local_z = xform(N, f3{b0, b1, b2});
-        f3 row2 = unit3(local_z);
+        f3 row2 = unit3_shared(local_z);
         // A rows: (v0.w v1.x v1.y), (v1.z v1.w v2.x), row2 — inverse by minors, each entry divided by det
         float m11 = v0.w, m12 = v1.x, m13 = v1.y, m21 = v1.z, m22 = v1.w, m23 = v2.x, m31 = row2.x, m32 = row2.y, m33 = row2.z;
         float mi1 = m22 * m33 - m32 * m23, mi2 = m21 * m33 - m31 * m23, mi3 = m21 * m32 - m31 * m22;
         float det = m11 * mi1 - m12 * mi2 + m13 * mi3;
         if (det == 0.0f) { atomicAdd(&a.diag[D_SINGULAR_BASIS], 1ull); return 0u; }
-        mat3 I = {{mi1 / det, (m13 * m32 - m33 * m12) / det, (m12 * m23 - m22 * m13) / det,
-                   -mi2 / det, (m11 * m33 - m31 * m13) / det, (m13 * m21 - m23 * m11) / det,
-                   mi3 / det, (m12 * m31 - m32 * m11) / det, (m11 * m22 - m21 * m12) / det}};
+        // every entry of the adjugate divided by det (nalgebra 3x3 try_inverse), one shared divisor
+        const float c12 = m13 * m32 - m33 * m12, c13 = m12 * m23 - m22 * m13, c22 = m11 * m33 - m31 * m13,
+                    c23 = m13 * m21 - m23 * m11, c32 = m12 * m31 - m32 * m11, c33 = m11 * m22 - m21 * m12;
+        mat3 I;
+        if (in_fast_division_range(det)) {
+            const SharedDivisor d = shared_divisor(det);
+            I = {{quotient(mi1, d), quotient(c12, d), quotient(c13, d), quotient(-mi2, d), quotient(c22, d), quotient(c23, d),
+                  quotient(mi3, d), quotient(c32, d), quotient(c33, d)}};
+        } else {
+            I = {{mi1 / det, c12 / det, c13 / det, -mi2 / det, c22 / det, c23 / det, mi3 / det, c32 / det, c33 / det}};
+        }
         // uvs: r2.z r2.w r3.x = u0 u1 u2 ; r3.y r3.z r3.w = v0 v1 v2
-        f3 lx = unit3(xform(I, f3{r2.w - r2.z, r3.x - r2.z, 0.0f}));
-        f3 ly = unit3(xform(I, f3{r3.z - r3.y, r3.w - r3.y, 0.0f}));
-        f3 lz = unit3(local_z);
+        f3 lx = unit3_shared(xform(I, f3{r2.w - r2.z, r3.x - r2.z, 0.0f}));
+        f3 ly = unit3_shared(xform(I, f3{r3.z - r3.y, r3.w - r3.y, 0.0f}));
+        f3 lz = unit3_shared(local_z);
         mat3 B = {{lx.x, ly.x, lz.x, lx.y, ly.y, lz.y, lx.z, ly.z, lz.z}};
-        f3 n = unit3(xform(B, nt));
+        f3 n = unit3_shared(xform(B, nt));
         diff = dot3(u.t_light, n);
     }
     return pack_rgb(blend_black(c.x, diff), blend_black(c.y, diff), blend_black(c.z, diff));

@@ -8,7 +8,7 @@ for cfg in "$@"; do
   rt=$1; tw=$2; th=$3; xf="${4:-}"
   touch tiny_renderer_b200/csrc/tinyr.cu
   make -s -C tiny_renderer_b200/csrc EXTRA="-DTR_RASTER_THREADS=$rt -DTR_TILE_W=$tw -DTR_TILE_H=$th $xf" all > /dev/null 2>&1 || { echo "build failed $cfg"; continue; }
-  python bench.py --steps 20 --warmup 3 > gpurun_out/tune_${rt}_${tw}_${th}.log 2>&1
+  python bench.py --steps 40 --warmup 3 > gpurun_out/tune_${rt}_${tw}_${th}.log 2>&1
   python - "$rt $tw $th" gpurun_out/tune_${rt}_${tw}_${th}.log <<'PY'
 import json,sys
 try:
