@@ -173,3 +173,23 @@ def test_shared_divisor_selftest(tinyr):
     for seed in (7, 0xC0FFEE):
         rc = tinyr.lib().tr_selftest_shared_divisor(0, 1 << 30, seed, ctypes.byref(bad))
         assert rc == 0 and bad.value == 0, (rc, bad.value)
+
+
+def test_large_polygons_literal_path(tinyr, oracle):
+    """Polygons whose bounding box exceeds kExactExtent (1024 px) take the literal f32 raster path (separate sweep):
+    two screen-filling triangles in front of / behind the model's own small ones, 3000x2000."""
+    from tiny_renderer_b200.scene import Model
+    m = get_model("african_head")
+    big = np.array([[-1.1, -1.1, -0.4], [1.1, -1.1, -0.2], [1.1, 1.1, 0.3], [-1.1, 1.1, 0.1]], np.float32)
+    pos = np.concatenate([m.positions, big])
+    v0 = len(m.positions)
+    quad = np.array([[v0, 0, 0, v0 + 1, 1, 1, v0 + 2, 2, 2], [v0, 0, 0, v0 + 2, 2, 2, v0 + 3, 3, 3]], np.uint32)
+    tri = np.concatenate([m.tri_idx[:1200], quad, m.tri_idx[1200:]])
+    model = Model(pos, m.uvs, m.normals, tri, m.maps, "head+quad")
+    for pipeline in ("phong", "shadow"):
+        g, o = parity.both(tinyr, oracle, model, pipeline, 3000, 2000, 0.3, 0.5)
+        st = parity.compare(g, o, two_pass=pipeline == "shadow", rgb_frac=1.0)
+        vis = g.raw_visibility()
+        assert ((vis == 1200) | (vis == 1201)).sum() > 10 ** 6          # the big polygons do win a large area
+        assert st["depth_bits_differ"] == 0
+        g.close()

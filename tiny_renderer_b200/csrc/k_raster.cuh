@@ -22,6 +22,7 @@
 // closures (k_shade.cuh); in depth-only mode the pass-1 fragment shaders of shadow / occlusion
 // (shader.rs:694-709, 832-847).
 #pragma once
+#include <type_traits>
 #include "k_shade.cuh"
 
 namespace tr {
@@ -62,7 +63,7 @@ struct RasterArgs {
 
 // Stage polygon t into slot: edge equations relative to the tile origin, or raw coordinates when inexact.
 __device__ __forceinline__ void stage_polygon(const RasterArgs& a, uint32_t t, int4 bb, int slot, int tx0, int ty0, int tx1, int ty1,
-                                              float* s_tri, int* s_lo, int* s_hi) {
+                                              float* s_tri, int* s_lo, int* s_hi, int* s_inexact) {
     const float4* r = a.rec + (size_t)t * 4;
     float4 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
     int x0 = __float_as_int(r0.x), y0 = __float_as_int(r0.y), x1 = __float_as_int(r0.z), y1 = __float_as_int(r0.w);
@@ -84,6 +85,8 @@ __device__ __forceinline__ void stage_polygon(const RasterArgs& a, uint32_t t, i
     } else {
         d[0] = make_int4(x0, y0, x1, y1);
         d[1] = make_int4(x2, y2, 0, (int)(id | kInexactFlag));
+        lo += kInexactRowBias; hi += kInexactRowBias;         // visible to the literal-path sweep only
+        atomicAdd(s_inexact, 1);
     }
     d[2] = make_int4(__float_as_int(r1.z), __float_as_int(r1.w), __float_as_int(r2.x), __float_as_int(1.0f / fabsf((float)d[1].z)));
     s_lo[slot] = lo;
@@ -102,6 +105,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     __shared__ int s_count;
     __shared__ int s_next;
     __shared__ int s_block;                                 // next block of the tile to hand to a warp
+    __shared__ int s_inexact;                               // staged polygons that need the literal f32 path
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // CTAs are handed out in launch order; tile_order lists the tiles from the screen centre outwards so that the
@@ -124,6 +128,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     const bool rgb_bulk = SHADE && sa.fresh;
     const int row_bytes = (tx1 - tx0 + 1) * 3;
 
+    const uint32_t epoch_hi = a.epoch << 24;
     const bool use_bin = n_bin <= (uint32_t)kBinCap;
     const uint32_t n_src = use_bin ? n_bin : a.n_triangles;
     bool from_memory = !cleared;                          // later rounds of a long list merge with the earlier ones
@@ -132,7 +137,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     bool more = n_src > 0;
     while (more) {
         // ---- (1) filter the source list (cell bin, or all polygons) against the tile, kListCap polygons per round ----
-        if (tid == 0) { s_count = 0; s_next = (int)n_src; s_block = 0; }
+        if (tid == 0) { s_count = 0; s_next = (int)n_src; s_block = 0; s_inexact = 0; }
         __syncthreads();
         for (uint32_t base = scan_from; base < n_src; base += kRasterThreads) {
             uint32_t i = base + tid, t = 0;
@@ -150,7 +155,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
             for (int w = 0; w < kRasterThreads / 32; ++w) { int c = s_warp_count[w]; if (w < warp) before += c; total += c; }
             int slot = before + __popc(m & ((1u << lane) - 1u));
             bool overflow = s_count + total > kListCap;
-            if (hit && slot < kListCap) stage_polygon(a, t, bb, slot, tx0, ty0, tx1, ty1, s_tri, s_lo, s_hi);
+            if (hit && slot < kListCap) stage_polygon(a, t, bb, slot, tx0, ty0, tx1, ty1, s_tri, s_lo, s_hi, &s_inexact);
             if (hit && slot >= kListCap) atomicMin(&s_next, (int)i);       // first source entry that did not fit
             __syncthreads();
             if (tid == 0) s_count = min(s_count + total, kListCap);
@@ -158,6 +163,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
             if (overflow) break;
         }
         const int n_list = s_count;
+        const int n_inexact = s_inexact;
         scan_from = (uint32_t)s_next;       // == n_src when everything was staged
         more = scan_from < n_src;
         if (n_list == 0) break;             // (more is false here: a round that staged nothing reached the end)
@@ -191,59 +197,69 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
                     else { unsigned long long key = a.keys[at]; bz[k] = key_depth(key); blo[k] = key_lo(key); }
                 }
             }
-            for (int base = 0; base < n_list; base += 32) {
-                int i = base + lane;
-                bool cand = false;
-                if (i < n_list) {
-                    int lo = s_lo[i], hi = s_hi[i];
-                    cand = (lo >> 16) <= bx0 + 7 && (hi >> 16) >= bx0 && (lo & 0xffff) <= by0 + kBlockH - 1 && (hi & 0xffff) >= by0;
-                }
-                unsigned m = __ballot_sync(0xffffffffu, cand);
-                while (m) {
-                    int j = base + __ffs(m) - 1;
-                    m &= m - 1;
-                    const int4* d = reinterpret_cast<const int4*>(s_tri + j * kStageWords);
-                    const int4 e = d[0], f = d[1];
-                    const bool exact = !((uint32_t)f.w & kInexactFlag);
-                    int e1[kPix], e2[kPix];
-                    bool inside[kPix], any = !exact;
-                    if (exact) {
-                        e1[0] = e.x + lx * e.y + ly * e.z;           // cx * sign(cz)
-                        e2[0] = e.w + lx * f.x + ly * f.y;           // cy * sign(cz)
+            // One sweep over the staged list: ballot the bounding boxes against the block, then every lane evaluates the
+            // candidates for its pixels.  Polygons too large for the integer path (kInexactFlag; rare) are staged with
+            // their rows offset by kInexactRowBias, so the exact sweep never sees them and a second, separate sweep runs
+            // the literal f32 path — two loop bodies, so the compiler cannot hoist the slow path's set-up into the hot one.
+            auto sweep = [&](auto exact_c) {
+                constexpr bool EXACT = decltype(exact_c)::value;
+                constexpr int kBias = EXACT ? 0 : kInexactRowBias;
+                for (int base = 0; base < n_list; base += 32) {
+                    int i = base + lane;
+                    bool cand = false;
+                    if (i < n_list) {
+                        int lo = s_lo[i], hi = s_hi[i];
+                        cand = (lo >> 16) <= bx0 + 7 && (hi >> 16) >= bx0 && (lo & 0xffff) <= by0 + kBlockH - 1 + kBias && (hi & 0xffff) >= by0 + kBias;
+                        if (!EXACT) cand = cand && (lo & 0xffff) >= kInexactRowBias && (lo & 0xffff) != 0x7fff;
+                    }
+                    unsigned m = __ballot_sync(0xffffffffu, cand);
+                    while (m) {
+                        int j = base + __ffs(m) - 1;
+                        m &= m - 1;
+                        const int4* d = reinterpret_cast<const int4*>(s_tri + j * kStageWords);
+                        const int4 e = d[0], f = d[1];
+                        int e1[kPix], e2[kPix];
+                        bool inside[kPix], any = !EXACT;
+                        if (EXACT) {
+                            e1[0] = e.x + lx * e.y + ly * e.z;           // cx * sign(cz)
+                            e2[0] = e.w + lx * f.x + ly * f.y;           // cy * sign(cz)
+#pragma unroll
+                            for (int k = 0; k < kPix; ++k) {
+                                if (k) { e1[k] = e1[k - 1] + 4 * e.z; e2[k] = e2[k - 1] + 4 * f.y; }
+                                inside[k] = ((f.z - e1[k] - e2[k]) | e1[k] | e2[k]) >= 0;
+                                any = any || inside[k];
+                            }
+                        }
+                        if (!any) continue;
+                        const int4 g = d[2];
+                        const uint32_t lo = epoch_hi | ((uint32_t)f.w & kTriMask);
 #pragma unroll
                         for (int k = 0; k < kPix; ++k) {
-                            if (k) { e1[k] = e1[k - 1] + 4 * e.z; e2[k] = e2[k - 1] + 4 * f.y; }
-                            inside[k] = ((f.z - e1[k] - e2[k]) | e1[k] | e2[k]) >= 0;
-                            any = any || inside[k];
-                        }
-                    }
-                    if (!any) continue;
-                    const int4 g = d[2];
-                    const uint32_t lo = (a.epoch << 24) | ((uint32_t)f.w & kTriMask);
-#pragma unroll
-                    for (int k = 0; k < kPix; ++k) {
-                        float z, b0, b1, b2;
-                        if (exact) {
-                            if (!inside[k]) continue;
-                            // (cx+cy)/cz, cx/cz, cy/cz of scene.rs:189-193: integer operands, 0 <= numerator <= |cz| <= 2^21
-                            const float cx = (float)e1[k], cy = (float)e2[k], cz = (float)f.z, rcz = __int_as_float(g.w);
-                            b0 = 1.0f - exact_quotient(cx + cy, cz, rcz); b1 = exact_quotient(cx, cz, rcz); b2 = exact_quotient(cy, cz, rcz);
-                            z = (b0 * __int_as_float(g.x) + b1 * __int_as_float(g.y)) + b2 * __int_as_float(g.z);
-                        } else {
-                            if (!fragment_depth(e.x, e.y, e.z, e.w, f.x, f.y, __int_as_float(g.x), __int_as_float(g.y), __int_as_float(g.z),
-                                                px, py + 4 * k, z, b0, b1, b2)) continue;
-                        }
-                        if (z != z) { atomicAdd(&a.diag[D_NAN_DEPTH], 1ull); continue; }
-                        if (DEPTH_ONLY) {
-                            if (z >= bz[k]) bz[k] = z;                               // shader.rs:703
-                        } else if (z > bz[k] || (z == bz[k] && lo < blo[k] && blo[k] != kNoTri)) {
-                            // shader.rs:175 `z <= zbuf -> reject`, applied in polygon order == key_beats() on packed keys
-                            bz[k] = z; blo[k] = lo;
-                            if (SHADE) { w0[k] = b0; w1[k] = b1; w2[k] = b2; fresh_winner[k] = true; }
+                            float z, b0, b1, b2;
+                            if (EXACT) {
+                                if (!inside[k]) continue;
+                                // (cx+cy)/cz, cx/cz, cy/cz of scene.rs:189-193: integer operands, 0 <= numerator <= |cz| <= 2^21
+                                const float cx = (float)e1[k], cy = (float)e2[k], cz = (float)f.z, rcz = __int_as_float(g.w);
+                                b0 = 1.0f - exact_quotient(cx + cy, cz, rcz); b1 = exact_quotient(cx, cz, rcz); b2 = exact_quotient(cy, cz, rcz);
+                                z = (b0 * __int_as_float(g.x) + b1 * __int_as_float(g.y)) + b2 * __int_as_float(g.z);
+                            } else {
+                                if (!fragment_depth(e.x, e.y, e.z, e.w, f.x, f.y, __int_as_float(g.x), __int_as_float(g.y), __int_as_float(g.z),
+                                                    px, py + 4 * k, z, b0, b1, b2)) continue;
+                            }
+                            if (z != z) { atomicAdd(&a.diag[D_NAN_DEPTH], 1ull); continue; }
+                            if (DEPTH_ONLY) {
+                                if (z >= bz[k]) bz[k] = z;                               // shader.rs:703
+                            } else if (z > bz[k] || (z == bz[k] && lo < blo[k] && blo[k] != kNoTri)) {
+                                // shader.rs:175 `z <= zbuf -> reject`, applied in polygon order == key_beats() on packed keys
+                                bz[k] = z; blo[k] = lo;
+                                if (SHADE) { w0[k] = b0; w1[k] = b1; w2[k] = b2; fresh_winner[k] = true; }
+                            }
                         }
                     }
                 }
-            }
+            };
+            sweep(std::true_type{});
+            if (n_inexact) sweep(std::false_type{});
 #pragma unroll
             for (int k = 0; k < kPix; ++k) {
                 if (!in[k]) continue;

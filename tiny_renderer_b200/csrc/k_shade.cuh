@@ -89,6 +89,7 @@ __device__ __forceinline__ uint32_t occlusion_gray(const float* shadow, const Un
     dl.w_zero += ok ? 0u : 1u;
     float fsv = shadow_lookup(shadow, fs, u.width, n_px, dl);
     float occ = 1.0f;
+    const SharedDivisor d20 = shared_divisor(20.0f);        // (sv - fsv) / 20.0 below: numerators in (1, ~300)
 #pragma unroll 4
     for (int k = 0; k < 16; ++k) {
         f3 sp = wp + u.ao_step[k];
@@ -96,7 +97,7 @@ __device__ __forceinline__ uint32_t occlusion_gray(const float* shadow, const Un
         dl.w_zero += ok ? 0u : 1u;
         float sv = shadow_lookup(shadow, sc, u.width, n_px, dl);
         if (sv - 1.0f > fsv) {
-            float strength = fminf((sv - fsv) / 20.0f, 1.0f);
+            float strength = fminf(quotient(sv - fsv, d20), 1.0f);
             occ -= 0.0625f * strength;
         }
     }
