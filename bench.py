@@ -200,10 +200,12 @@ def algorithmic_bytes(n_px, covered, n_tri, pipe):
 
 def ncu_traffic(pipe):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused tile kernel, from the committed
-    `ncu --set full` capture (profiles/r1d_traffic.json); None when the file is absent."""
-    p = os.path.join(ROOT, "profiles", "r1d_traffic.json")
-    if not os.path.exists(p):
+    newest `ncu --set full` summary (profiles/r1?_traffic.json, written by tools/ncu_summary.py); None when absent."""
+    import glob
+    found = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))
+    if not found:
         return None
+    p = found[-1]
     want = "k_raster<%d>" % {"phong": 1, "darboux": 4}[pipe]
     with open(p) as f:
         for k, v in json.load(f).items():

@@ -2,8 +2,9 @@
 //
 // One CTA owns one kTileW x kTileH screen tile.  (1) It filters the polygon list of the binning cell the tile lies
 // in (K1+K2; a scan of all bounding boxes when the cell's bin overflowed) against the tile and stages per-polygon
-// edge equations in shared memory.  (2) Warps pull 8x8-pixel blocks off the tile, two pixels per lane: 32 lanes test
-// 32 staged bounding boxes against the block, a ballot yields the candidate mask, and every lane evaluates the
+// edge equations in shared memory, together with a 32-bit mask of the 8x8-pixel blocks of the tile the triangle
+// can reach (bounding box, narrowed by the three edge functions' maxima per block).  (2) Warps pull blocks off the
+// tile, two pixels per lane: 32 lanes test the block's bit of 32 masks, a ballot yields the candidates, and every lane evaluates the
 // inside test for its own pixel with operands broadcast from shared memory.  Visibility is resolved in registers —
 // (depth, epoch|polygon) compared the way a 64-bit atomicMin on the packed key would order them, without the L2
 // round trips — and the key of every pixel of a touched tile is written once.  (3) In the shading modes the lane
@@ -61,18 +62,63 @@ struct RasterArgs {
     unsigned long long* diag;
 };
 
-// Stage polygon t into slot: edge equations relative to the tile origin, or raw coordinates when inexact.
+// The tile is cut into kBlocksX x kBlocksY blocks of 8 x kBlockH pixels (one warp pass each); bit (by * kBlocksX + bx)
+// of a block mask stands for block (bx, by).
+constexpr int kPix = TR_PIXELS_PER_LANE;                // pixels per lane in the block loop (1 or 2), 4 rows apart
+constexpr int kBlockH = 4 * kPix;
+constexpr int kBlocksX = kTileW / 8;
+constexpr int kBlocksY = kTileH / kBlockH;
+constexpr int kBlocks = kBlocksX * kBlocksY;
+static_assert(kPix == 1 || kPix == 2, "the fragment stage selects between at most two pixels per lane");
+static_assert(kTileH % kBlockH == 0 && kTileW % 8 == 0, "tiles must hold whole blocks");
+static_assert(kBlocks <= 32, "one 32-bit block mask per staged polygon");
+
+// Blocks a tile-relative, clamped, inclusive bounding box overlaps.
+__device__ __forceinline__ uint32_t bbox_block_mask(int lx0, int ly0, int lx1, int ly1) {
+    const int bx0 = lx0 >> 3, bx1 = lx1 >> 3, by0 = ly0 / kBlockH, by1 = ly1 / kBlockH;
+    uint32_t rep = 0;
+#pragma unroll
+    for (int r = 0; r < kBlocksY; ++r) rep |= 1u << (r * kBlocksX);
+    const uint32_t cols = (2u << bx1) - (1u << bx0);
+    const int lo = kBlocksX * by0, hi = kBlocksX * (by1 + 1) - 1;
+    return (cols * rep) & (0xffffffffu >> (31 - hi)) & (0xffffffffu << lo);
+}
+
+// Blocks that can hold an inside pixel of an exact-path polygon: with e1, e2 the staged edge functions and
+// e0 = cz - e1 - e2, a pixel is inside iff all three are >= 0 (see the sweep below); each is linear in the pixel, so
+// its largest value over a block sits at one corner, and a block where any of the three maxima is negative holds no
+// inside pixel.  Integer arithmetic throughout (|values| < 2^23), hence conservative AND exact.
+__device__ __forceinline__ uint32_t edge_block_mask(int4 e, int4 f) {
+    const int a1 = e.y, b1 = e.z, a2 = f.x, b2 = f.y, a0 = -(a1 + a2), b0 = -(b1 + b2);
+    const int m0 = (f.z - e.x - e.w) + 7 * max(a0, 0) + (kBlockH - 1) * max(b0, 0);
+    const int m1 = e.x + 7 * max(a1, 0) + (kBlockH - 1) * max(b1, 0);
+    const int m2 = e.w + 7 * max(a2, 0) + (kBlockH - 1) * max(b2, 0);
+    uint32_t outside = 0;                   // one bit per block pushed in from the right: block 0 ends up leftmost
+#pragma unroll
+    for (int by = 0; by < kBlocksY; ++by) {
+        int v0 = m0 + by * kBlockH * b0, v1 = m1 + by * kBlockH * b1, v2 = m2 + by * kBlockH * b2;
+#pragma unroll
+        for (int bx = 0; bx < kBlocksX; ++bx) {
+            outside = __funnelshift_l((uint32_t)(v0 | v1 | v2), outside, 1);      // sign bit: some maximum is negative
+            v0 += 8 * a0; v1 += 8 * a1; v2 += 8 * a2;
+        }
+    }
+    return ~(__brev(outside) >> (32 - kBlocks));
+}
+
+// Stage polygon t into slot: edge equations relative to the tile origin, or raw coordinates when inexact.  s_mask /
+// s_maskx receive the blocks its bounding box overlaps (exact path / literal path; the other one is 0).
 __device__ __forceinline__ void stage_polygon(const RasterArgs& a, uint32_t t, int4 bb, int slot, int tx0, int ty0, int tx1, int ty1,
-                                              float* s_tri, int* s_lo, int* s_hi, int* s_inexact) {
+                                              float* s_tri, uint32_t* s_mask, uint32_t* s_maskx, int* s_inexact) {
     const float4* r = a.rec + (size_t)t * 4;
     float4 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
     int x0 = __float_as_int(r0.x), y0 = __float_as_int(r0.y), x1 = __float_as_int(r0.z), y1 = __float_as_int(r0.w);
     int x2 = __float_as_int(r1.x), y2 = __float_as_int(r1.y);
     long long ex = (long long)max(max(x0, x1), x2) - min(min(x0, x1), x2), ey = (long long)max(max(y0, y1), y2) - min(min(y0, y1), y2);
     int4* d = reinterpret_cast<int4*>(s_tri + slot * kStageWords);
-    int lo = ((max(bb.x, tx0) - tx0) << 16) | (max(bb.y, ty0) - ty0);
-    int hi = ((min(bb.z, tx1) - tx0) << 16) | (min(bb.w, ty1) - ty0);
+    uint32_t blocks = bbox_block_mask(max(bb.x, tx0) - tx0, max(bb.y, ty0) - ty0, min(bb.z, tx1) - tx0, min(bb.w, ty1) - ty0);
     uint32_t id = t;
+    bool exact = true;
     if (ex <= kExactExtent && ey <= kExactExtent) {
         int ux = x1 - x0, uy = x2 - x0, vx = y1 - y0, vy = y2 - y0;
         int cz = ux * vy - uy * vx;
@@ -81,16 +127,16 @@ __device__ __forceinline__ void stage_polygon(const RasterArgs& a, uint32_t t, i
         // cx(lx,ly) = uy*(y0-py) - (x0-px)*vy ,  cy(lx,ly) = (x0-px)*vx - ux*(y0-py)   with px = tx0+lx, py = ty0+ly
         d[0] = make_int4(s * (uy * ry - rx * vy), s * vy, -s * uy, s * (rx * vx - ux * ry));
         d[1] = make_int4(-s * vx, s * ux, s * cz, (int)id);
-        if (cz == 0) { lo = 0x7fff7fff; hi = 0; }       // |cz| < 1: degenerate, never produces a fragment (scene.rs:188)
+        if (cz == 0) blocks = 0u;                       // |cz| < 1: degenerate, never produces a fragment (scene.rs:188)
     } else {
         d[0] = make_int4(x0, y0, x1, y1);
         d[1] = make_int4(x2, y2, 0, (int)(id | kInexactFlag));
-        lo += kInexactRowBias; hi += kInexactRowBias;         // visible to the literal-path sweep only
+        exact = false;                                  // visible to the literal-path sweep only
         atomicAdd(s_inexact, 1);
     }
     d[2] = make_int4(__float_as_int(r1.z), __float_as_int(r1.w), __float_as_int(r2.x), __float_as_int(1.0f / fabsf((float)d[1].z)));
-    s_lo[slot] = lo;
-    s_hi[slot] = hi;
+    s_mask[slot] = exact ? blocks : 0u;
+    s_maskx[slot] = exact ? 0u : blocks;
 }
 
 template <int MODE>
@@ -99,7 +145,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     constexpr bool SHADE = MODE >= 0;
     constexpr int kRgbRow = kTileW * 3;
     __shared__ __align__(16) float s_tri[kListCap * kStageWords];
-    __shared__ int s_lo[kListCap], s_hi[kListCap];
+    __shared__ uint32_t s_mask[kListCap], s_maskx[kListCap];   // per staged polygon: blocks to visit (exact / literal path)
     __shared__ __align__(16) uint8_t s_rgb[SHADE ? kTileH * kRgbRow : 16];
     __shared__ int s_warp_count[kRasterThreads / 32];
     __shared__ int s_count;
@@ -114,12 +160,6 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     const int tx0 = (int)(tile % a.tiles_x) * kTileW, ty0 = (int)(tile / a.tiles_x) * kTileH;
     const int tx1 = min(tx0 + kTileW, (int)a.width) - 1, ty1 = min(ty0 + kTileH, (int)a.height) - 1;
     const float kFloatMin = -3.402823466e38f;
-    constexpr int kPix = TR_PIXELS_PER_LANE;                // pixels per lane in the block loop (1 or 2)
-    constexpr int kBlockH = 4 * kPix;
-    constexpr int kBlocksX = kTileW / 8;
-    constexpr int kBlocks = kBlocksX * (kTileH / kBlockH);
-    static_assert(kPix == 1 || kPix == 2, "the fragment stage selects between at most two pixels per lane");
-    static_assert(kTileH % kBlockH == 0, "tile height must hold whole blocks");
 
     const uint32_t cell = (uint32_t)(ty0 / kCellH) * a.bins.cells_x + (uint32_t)(tx0 / kCellW);
     const uint32_t n_bin = a.bins.count[a.bins.parity * a.bins.n_cells + cell];
@@ -155,7 +195,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
             for (int w = 0; w < kRasterThreads / 32; ++w) { int c = s_warp_count[w]; if (w < warp) before += c; total += c; }
             int slot = before + __popc(m & ((1u << lane) - 1u));
             bool overflow = s_count + total > kListCap;
-            if (hit && slot < kListCap) stage_polygon(a, t, bb, slot, tx0, ty0, tx1, ty1, s_tri, s_lo, s_hi, &s_inexact);
+            if (hit && slot < kListCap) stage_polygon(a, t, bb, slot, tx0, ty0, tx1, ty1, s_tri, s_mask, s_maskx, &s_inexact);
             if (hit && slot >= kListCap) atomicMin(&s_next, (int)i);       // first source entry that did not fit
             __syncthreads();
             if (tid == 0) s_count = min(s_count + total, kListCap);
@@ -168,6 +208,17 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         more = scan_from < n_src;
         if (n_list == 0) break;             // (more is false here: a round that staged nothing reached the end)
         touched = true;
+        // Narrow the bounding-box masks of the exact-path polygons to the blocks the triangle itself reaches (one lane
+        // per staged polygon), and pad both mask arrays with zeros to a whole warp for the sweeps below.
+        for (int i = tid; i < ((n_list + 31) & ~31); i += kRasterThreads) {
+            if (i >= n_list) { s_mask[i] = 0u; s_maskx[i] = 0u; continue; }
+            const uint32_t m = s_mask[i];
+            if (m) {
+                const int4* d = reinterpret_cast<const int4*>(s_tri + i * kStageWords);
+                s_mask[i] = m & edge_block_mask(d[0], d[1]);
+            }
+        }
+        __syncthreads();
 
         // ---- (2) warps pull 8 x (4*kPix) blocks off the tile (a lane owns kPix pixels, 4 rows apart); ballot the staged
         //      bboxes against the block, evaluate per pixel ----
@@ -197,22 +248,15 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
                     else { unsigned long long key = a.keys[at]; bz[k] = key_depth(key); blo[k] = key_lo(key); }
                 }
             }
-            // One sweep over the staged list: ballot the bounding boxes against the block, then every lane evaluates the
-            // candidates for its pixels.  Polygons too large for the integer path (kInexactFlag; rare) are staged with
-            // their rows offset by kInexactRowBias, so the exact sweep never sees them and a second, separate sweep runs
-            // the literal f32 path — two loop bodies, so the compiler cannot hoist the slow path's set-up into the hot one.
+            // One sweep over the staged list: ballot the block's bit of the polygons' block masks, then every lane
+            // evaluates the candidates for its pixels.  Polygons too large for the integer path (kInexactFlag; rare) carry
+            // their mask in s_maskx, so the exact sweep never sees them and a second, separate sweep runs the literal f32
+            // path — two loop bodies, so the compiler cannot hoist the slow path's set-up into the hot one.
             auto sweep = [&](auto exact_c) {
                 constexpr bool EXACT = decltype(exact_c)::value;
-                constexpr int kBias = EXACT ? 0 : kInexactRowBias;
+                const uint32_t* masks = EXACT ? s_mask : s_maskx;
                 for (int base = 0; base < n_list; base += 32) {
-                    int i = base + lane;
-                    bool cand = false;
-                    if (i < n_list) {
-                        int lo = s_lo[i], hi = s_hi[i];
-                        cand = (lo >> 16) <= bx0 + 7 && (hi >> 16) >= bx0 && (lo & 0xffff) <= by0 + kBlockH - 1 + kBias && (hi & 0xffff) >= by0 + kBias;
-                        if (!EXACT) cand = cand && (lo & 0xffff) >= kInexactRowBias && (lo & 0xffff) != 0x7fff;
-                    }
-                    unsigned m = __ballot_sync(0xffffffffu, cand);
+                    unsigned m = __ballot_sync(0xffffffffu, (masks[base + lane] >> blk) & 1u);
                     while (m) {
                         int j = base + __ffs(m) - 1;
                         m &= m - 1;
