@@ -57,7 +57,7 @@ struct RasterArgs {
     // is stale.  Scene::clear therefore costs nothing for tiles no polygon touches; K6 and the getters never read
     // their keys.
     uint32_t* tile_state;
-    const uint32_t* tile_order;   // launch position -> tile index (null = identity)
+    const uint32_t* tile_order;   // launch position -> tile coordinates, y << 16 | x
     float* depth;              // depth-only mode (shadow buffer)
     unsigned long long* diag;
 };
@@ -154,10 +154,11 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     __shared__ int s_inexact;                               // staged polygons that need the literal f32 path
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // CTAs are handed out in launch order; tile_order lists the tiles from the screen centre outwards so that the
-    // tiles that usually carry the geometry start first and the cheap border tiles fill the tail of the grid.
-    const uint32_t tile = a.tile_order ? __ldg(&a.tile_order[blockIdx.x]) : blockIdx.x;
-    const int tx0 = (int)(tile % a.tiles_x) * kTileW, ty0 = (int)(tile / a.tiles_x) * kTileH;
+    // CTAs are handed out in launch order; for a lone frame tile_order lists the tiles from the screen centre outwards
+    // so that the tiles that usually carry the geometry start first and the cheap border tiles fill the tail of the grid.
+    const uint32_t tile_xy = __ldg(&a.tile_order[blockIdx.x]);
+    const uint32_t tile = (tile_xy >> 16) * a.tiles_x + (tile_xy & 0xffffu);
+    const int tx0 = (int)(tile_xy & 0xffffu) * kTileW, ty0 = (int)(tile_xy >> 16) * kTileH;
     const int tx1 = min(tx0 + kTileW, (int)a.width) - 1, ty1 = min(ty0 + kTileH, (int)a.height) - 1;
     const float kFloatMin = -3.402823466e38f;
 
@@ -169,6 +170,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     const int row_bytes = (tx1 - tx0 + 1) * 3;
 
     const uint32_t epoch_hi = a.epoch << 24;
+    const uint32_t s_block_at = (uint32_t)__cvta_generic_to_shared(&s_block);
     const bool use_bin = n_bin <= (uint32_t)kBinCap;
     const uint32_t n_src = use_bin ? n_bin : a.n_triangles;
     bool from_memory = !cleared;                          // later rounds of a long list merge with the earlier ones
@@ -226,8 +228,8 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         for (int blk = warp; blk < kBlocks; blk += kRasterThreads / 32) {
 #else
         for (;;) {
-            int blk = 0;
-            if (lane == 0) blk = atomicAdd(&s_block, 1);
+            int blk = 0;         // (plain PTX: the compiler wraps atomicAdd in a warp-aggregation sequence even for one lane)
+            if (lane == 0) asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(blk) : "r"(s_block_at) : "memory");
             blk = __shfl_sync(0xffffffffu, blk, 0);
             if (blk >= kBlocks) break;
 #endif
@@ -352,9 +354,18 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         // Nothing touches this tile: an uncleared target keeps its contents, a cleared one its cleared state.
         if (cleared) {
             if (DEPTH_ONLY) {
-                for (int i = tid; i < kTileW * kTileH; i += kRasterThreads) {
-                    int px = tx0 + i % kTileW, py = ty0 + i / kTileW;
-                    if (px < (int)a.width && py < (int)a.height) a.depth[(size_t)py * a.width + px] = kFloatMin;
+                if ((a.width & 3u) == 0u) {                 // rows of the tile are 16-byte aligned and whole float4s
+                    const int quads = (tx1 - tx0 + 1) >> 2;
+                    const float4 v = make_float4(kFloatMin, kFloatMin, kFloatMin, kFloatMin);
+                    const int c = tid % (kTileW / 4);
+                    if (c < quads)
+                        for (int r = tid / (kTileW / 4); r <= ty1 - ty0; r += kRasterThreads / (kTileW / 4))
+                            reinterpret_cast<float4*>(a.depth + (size_t)(ty0 + r) * a.width + tx0)[c] = v;
+                } else {
+                    for (int i = tid; i < kTileW * kTileH; i += kRasterThreads) {
+                        int px = tx0 + i % kTileW, py = ty0 + i / kTileW;
+                        if (px < (int)a.width && py < (int)a.height) a.depth[(size_t)py * a.width + px] = kFloatMin;
+                    }
                 }
             } else if (tid == 0) {
                 a.tile_state[tile] = 1u;
@@ -369,12 +380,17 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         const int rows = ty1 - ty0 + 1;
         if ((a.width & 15u) == 0u) {
             const int vec_per_row = row_bytes >> 4;             // tile widths are multiples of 16 px here; <= 12 vectors
-            const int c = tid & 15;
+            const int c = tid & 15, r0 = tid >> 4;
             if (c < vec_per_row) {
-                for (int r = tid >> 4; r < rows; r += kRasterThreads / 16) {
-                    uint4 v = touched ? *reinterpret_cast<const uint4*>(s_rgb + r * kRgbRow + c * 16) : make_uint4(0u, 0u, 0u, 0u);
-                    uint8_t* dst = sa.rgb + ((size_t)(a.height - 1 - (ty0 + r)) * a.width + tx0) * 3;
-                    reinterpret_cast<uint4*>(dst)[c] = v;
+                constexpr int kStep = kRasterThreads / 16;
+                uint8_t* dst = sa.rgb + ((size_t)(a.height - 1 - (ty0 + r0)) * a.width + tx0) * 3 + c * 16;
+                const ptrdiff_t dst_step = -(ptrdiff_t)kStep * a.width * 3;
+                const uint8_t* src = s_rgb + r0 * kRgbRow + c * 16;
+                if (touched) {
+                    for (int r = r0; r < rows; r += kStep, dst += dst_step, src += kStep * kRgbRow)
+                        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+                } else {
+                    for (int r = r0; r < rows; r += kStep, dst += dst_step) *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
                 }
             }
         } else {

@@ -55,7 +55,9 @@ struct tr_scene {
     };
     std::vector<Slot> slots;
     uint32_t tiles_x = 0, tiles_y = 0;
-    uint32_t* tile_order = nullptr;      // tiles sorted by distance from the screen centre (launch order of K3/K4)
+    // launch position -> tile coordinates (y << 16 | x), two orders of n_tiles entries each: [0] tiles sorted by
+    // distance from the screen centre, [1] plain row order
+    uint32_t* tile_order = nullptr;
     bool overlapping = false;            // a batch is running frames / light passes concurrently on the slot streams
     uint32_t* ao = nullptr;
     AoList ao_list{};                  // covered pixels of the camera view (many-light AO batch), allocated on first use
@@ -244,8 +246,13 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
             return dx * dx + dy * dy;
         };
         std::stable_sort(order.begin(), order.end(), [&](uint32_t p, uint32_t q) { return dist(p) < dist(q); });
-        CU(cudaMalloc(&s->tile_order, n_tiles * 4));
-        CU(cudaMemcpy(s->tile_order, order.data(), n_tiles * 4, cudaMemcpyHostToDevice));
+        std::vector<uint32_t> packed(2 * n_tiles);
+        for (size_t i = 0; i < n_tiles; ++i) {
+            packed[i] = ((order[i] / s->tiles_x) << 16) | (order[i] % s->tiles_x);
+            packed[n_tiles + i] = ((uint32_t)(i / s->tiles_x) << 16) | (uint32_t)(i % s->tiles_x);
+        }
+        CU(cudaMalloc(&s->tile_order, packed.size() * 4));
+        CU(cudaMemcpy(s->tile_order, packed.data(), packed.size() * 4, cudaMemcpyHostToDevice));
     }
     s->slots.assign(s->ring, tr_scene::Slot{});
     for (uint32_t r = 0; r < s->ring; ++r) {
@@ -341,7 +348,7 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     ShadeArgs sa = shade_args(s, fresh_rgb);
     // centre-out launch order shortens a lone frame's tail; overlapped batches do better in plain row order, where one
     // frame's cheap border tiles run beside the previous frame's heavy ones (measured: profiles/README.md)
-    a.tile_order = s->overlapping ? nullptr : s->tile_order;
+    a.tile_order = s->tile_order + (s->overlapping ? (size_t)s->tiles_x * s->tiles_y : 0);
     dim3 grid(s->tiles_x * s->tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
 #define TR_RASTER(M) k_raster<M><<<grid, kRasterThreads, 0, s->stream>>>(a, sa, u)
