@@ -24,6 +24,7 @@
 // (shader.rs:694-709, 832-847).
 #pragma once
 #include <type_traits>
+#include <cuda.h>               // CUtensorMap
 #include "k_shade.cuh"
 
 namespace tr {
@@ -59,6 +60,7 @@ struct RasterArgs {
     uint32_t* tile_state;
     const uint32_t* tile_order;   // launch position -> tile coordinates, y << 16 | x
     float* depth;              // depth-only mode (shadow buffer)
+    uint32_t* depth_clear;     // depth-only mode, per tile: nonzero = every depth of the tile holds the cleared value already
     unsigned long long* diag;
 };
 
@@ -139,14 +141,34 @@ __device__ __forceinline__ void stage_polygon(const RasterArgs& a, uint32_t t, i
     s_maskx[slot] = exact ? 0u : blocks;
 }
 
+// Winner state of a lane's pixels as left in memory by earlier work on the target (a render without clear, or an
+// earlier round of a long polygon list).  Out of line on purpose: inlined, the compiler predicates these loads and
+// conversions into every block's start-up, where a cleared frame — the common case — never needs them.
+struct BlockState { float z[kPix]; uint32_t lo[kPix]; };
+template <bool DEPTH_ONLY>
+__device__ __noinline__ BlockState load_block_state(const unsigned long long* keys, const float* depth, int width, int height, int px, int py) {
+    BlockState st;
+#pragma unroll
+    for (int k = 0; k < kPix; ++k) {
+        st.z[k] = -3.402823466e38f; st.lo[k] = kNoTri;
+        if (px < width && py + 4 * k < height) {
+            const size_t at = (size_t)(py + 4 * k) * width + px;
+            if (DEPTH_ONLY) st.z[k] = depth[at];
+            else { unsigned long long key = keys[at]; st.z[k] = key_depth(key); st.lo[k] = key_lo(key); }
+        }
+    }
+    return st;
+}
+
 template <int MODE>
-__global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u) {
+__global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u, const __grid_constant__ CUtensorMap rgb_map) {
     constexpr bool DEPTH_ONLY = MODE == kModeDepthOnly;
     constexpr bool SHADE = MODE >= 0;
     constexpr int kRgbRow = kTileW * 3;
     __shared__ __align__(16) float s_tri[kListCap * kStageWords];
     __shared__ uint32_t s_mask[kListCap], s_maskx[kListCap];   // per staged polygon: blocks to visit (exact / literal path)
-    __shared__ __align__(16) uint8_t s_rgb[SHADE ? kTileH * kRgbRow : 16];
+    // the tile's RGB in frame order (top-down: tile row r at s_rgb row kTileH-1-r), the box of the TMA store
+    __shared__ __align__(128) uint8_t s_rgb[SHADE ? kTileH * kRgbRow : 16];
     __shared__ int s_warp_count[kRasterThreads / 32];
     __shared__ int s_count;
     __shared__ int s_next;
@@ -228,8 +250,10 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         for (int blk = warp; blk < kBlocks; blk += kRasterThreads / 32) {
 #else
         for (;;) {
-            int blk = 0;         // (plain PTX: the compiler wraps atomicAdd in a warp-aggregation sequence even for one lane)
-            if (lane == 0) asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(blk) : "r"(s_block_at) : "memory");
+            // (the assembler wraps an atomic add in a ~15-instruction warp-aggregation sequence even for one lane; the
+            // wrapping increment stays a single ATOMS.INC)
+            int blk = 0;
+            if (lane == 0) asm volatile("atom.shared.inc.u32 %0, [%1], 0x7fffffff;" : "=r"(blk) : "r"(s_block_at) : "memory");
             blk = __shfl_sync(0xffffffffu, blk, 0);
             if (blk >= kBlocks) break;
 #endif
@@ -239,16 +263,13 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
             // running winners: depth, low key word (epoch | polygon; kNoTri = nothing drawn yet) and barycentrics
             float bz[kPix], w0[kPix], w1[kPix], w2[kPix];
             uint32_t blo[kPix];
-            bool in[kPix], fresh_winner[kPix];      // fresh: the winner was found in this round (w0..w2 are its barycentrics)
+            bool fresh_winner[kPix];                // the winner was found in this round (w0..w2 are its barycentrics)
 #pragma unroll
-            for (int k = 0; k < kPix; ++k) {
-                in[k] = px < (int)a.width && py + 4 * k < (int)a.height;
-                bz[k] = kFloatMin; blo[k] = kNoTri; w0[k] = w1[k] = w2[k] = 0.0f; fresh_winner[k] = false;
-                if (from_memory && in[k]) {
-                    const size_t at = (size_t)(py + 4 * k) * a.width + px;
-                    if (DEPTH_ONLY) bz[k] = a.depth[at];
-                    else { unsigned long long key = a.keys[at]; bz[k] = key_depth(key); blo[k] = key_lo(key); }
-                }
+            for (int k = 0; k < kPix; ++k) { bz[k] = kFloatMin; blo[k] = kNoTri; w0[k] = w1[k] = w2[k] = 0.0f; fresh_winner[k] = false; }
+            if (from_memory) {
+                const BlockState st = load_block_state<DEPTH_ONLY>(a.keys, a.depth, (int)a.width, (int)a.height, px, py);
+#pragma unroll
+                for (int k = 0; k < kPix; ++k) { bz[k] = st.z[k]; blo[k] = st.lo[k]; }
             }
             // One sweep over the staged list: ballot the block's bit of the polygons' block masks, then every lane
             // evaluates the candidates for its pixels.  Polygons too large for the integer path (kInexactFlag; rare) carry
@@ -308,24 +329,28 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
             if (n_inexact) sweep(std::false_type{});
 #pragma unroll
             for (int k = 0; k < kPix; ++k) {
-                if (!in[k]) continue;
-                const size_t at = (size_t)(py + 4 * k) * a.width + px;
-                if (DEPTH_ONLY) a.depth[at] = bz[k];
-                else a.keys[at] = make_key(bz[k], blo[k]);
+                if (px < (int)a.width && py + 4 * k < (int)a.height) {
+                    const size_t at = (size_t)(py + 4 * k) * a.width + px;
+                    if (DEPTH_ONLY) a.depth[at] = bz[k];
+                    else a.keys[at] = make_key(bz[k], blo[k]);
+                } else {
+                    blo[k] = kNoTri;                // off-screen lanes of a border tile: nothing to shade below
+                }
             }
             if (SHADE && !more) {
                 // ---- (3) fragment stage for the winners that passed the depth test in THIS render; one copy of the
                 //      fragment code (the pixel's state is selected into scalars) keeps the kernel in the instruction cache
+                uint8_t* const tile_px = s_rgb + (kTileH - 1 - ly) * kRgbRow + lx * 3;
 #pragma unroll 1
                 for (int k = 0; k < kPix; ++k) {
                     const bool second = k != 0;
                     float z = bz[0], v0 = w0[0], v1 = w1[0], v2 = w2[0];
                     uint32_t lo = blo[0];
-                    bool pin = in[0], fresh = fresh_winner[0];
-                    if (kPix > 1 && second) { z = bz[kPix - 1]; v0 = w0[kPix - 1]; v1 = w1[kPix - 1]; v2 = w2[kPix - 1]; lo = blo[kPix - 1]; pin = in[kPix - 1]; fresh = fresh_winner[kPix - 1]; }
-                    const int qy = py + 4 * k, sy = ly + 4 * k;
+                    bool fresh = fresh_winner[0];
+                    if (kPix > 1 && second) { z = bz[kPix - 1]; v0 = w0[kPix - 1]; v1 = w1[kPix - 1]; v2 = w2[kPix - 1]; lo = blo[kPix - 1]; fresh = fresh_winner[kPix - 1]; }
+                    const int qy = py + 4 * k;
                     uint32_t out = 0u;
-                    const bool shaded = pin && lo != kNoTri && (lo >> 24) == a.epoch;
+                    const bool shaded = lo != kNoTri && (lo >> 24) == a.epoch;
                     if (shaded) {
                         if (!fresh) {           // won in an earlier round of a long list: re-derive its barycentrics
                             const float4* r = a.rec + (size_t)(lo & kTriMask) * 4;
@@ -337,7 +362,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
                         out = shade_pixel<SHADE ? MODE : 0>(sa, u, lo & kTriMask, px, qy, z, v0, v1, v2);
                     }
                     if (rgb_bulk) {
-                        uint8_t* p = s_rgb + sy * kRgbRow + lx * 3;
+                        uint8_t* p = tile_px - k * (4 * kRgbRow);
                         p[0] = (uint8_t)out; p[1] = (uint8_t)(out >> 8); p[2] = (uint8_t)(out >> 16);
                     } else if (shaded) {
                         uint8_t* p = sa.rgb + ((size_t)(a.height - 1 - qy) * a.width + px) * 3;
@@ -347,6 +372,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
             }
         }
         from_memory = true;
+        if (SHADE) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // s_rgb -> the TMA store below
         __syncthreads();
     }
 
@@ -354,6 +380,9 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         // Nothing touches this tile: an uncleared target keeps its contents, a cleared one its cleared state.
         if (cleared) {
             if (DEPTH_ONLY) {
+                if (a.depth_clear[tile] != 0u) return;      // still cleared from an earlier pass: nothing to write
+                __syncthreads();                            // (every warp has read the flag before it changes)
+                if (tid == 0) a.depth_clear[tile] = 1u;
                 if ((a.width & 3u) == 0u) {                 // rows of the tile are 16-byte aligned and whole float4s
                     const int quads = (tx1 - tx0 + 1) >> 2;
                     const float4 v = make_float4(kFloatMin, kFloatMin, kFloatMin, kFloatMin);
@@ -371,35 +400,39 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
                 a.tile_state[tile] = 1u;
             }
         }
-    } else if (!DEPTH_ONLY && tid == 0) {
-        a.tile_state[tile] = 0u;
+    } else if (tid == 0) {
+        if (DEPTH_ONLY) a.depth_clear[tile] = 0u;
+        else a.tile_state[tile] = 0u;
     }
 
     if (rgb_bulk) {
-        // ---- (4) the tile's RGB, top-down rows, 16-byte stores when the frame layout allows ----
-        const int rows = ty1 - ty0 + 1;
-        if ((a.width & 15u) == 0u) {
-            const int vec_per_row = row_bytes >> 4;             // tile widths are multiples of 16 px here; <= 12 vectors
-            const int c = tid & 15, r0 = tid >> 4;
-            if (c < vec_per_row) {
-                constexpr int kStep = kRasterThreads / 16;
-                uint8_t* dst = sa.rgb + ((size_t)(a.height - 1 - (ty0 + r0)) * a.width + tx0) * 3 + c * 16;
-                const ptrdiff_t dst_step = -(ptrdiff_t)kStep * a.width * 3;
-                const uint8_t* src = s_rgb + r0 * kRgbRow + c * 16;
-                if (touched) {
-                    for (int r = r0; r < rows; r += kStep, dst += dst_step, src += kStep * kRgbRow)
-                        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
-                } else {
-                    for (int r = r0; r < rows; r += kStep, dst += dst_step) *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
-                }
+        // ---- (4) the tile's RGB: one TMA tensor store of the kTileW x kTileH box (clipped at the frame border by the
+        //      hardware).  A tile nothing touches is all zeros; when it already was, nothing is written at all.
+        if (!touched && sa.rgb_zero[tile] != 0u) return;
+        if (!touched) {
+            for (int i = tid; i < kTileH * kRgbRow / 16; i += kRasterThreads) reinterpret_cast<uint4*>(s_rgb)[i] = make_uint4(0u, 0u, 0u, 0u);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+        }
+        if (sa.rgb_tma) {
+            if (tid == 0) {
+                const uint32_t src = (uint32_t)__cvta_generic_to_shared(s_rgb);
+                const int x = tx0 * 3, y = (int)a.height - ty0 - kTileH;        // y < 0 on a partial top tile row: clipped
+                asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                             :: "l"(reinterpret_cast<uint64_t>(&rgb_map)), "r"(src), "r"(x), "r"(y) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             }
         } else {
+            const int rows = ty1 - ty0 + 1;
             for (int i = tid; i < rows * row_bytes; i += kRasterThreads) {
                 int r = i / row_bytes, c = i % row_bytes;
-                uint8_t* dst = sa.rgb + ((size_t)(a.height - 1 - (ty0 + r)) * a.width + tx0) * 3;
-                dst[c] = touched ? s_rgb[r * kRgbRow + c] : (uint8_t)0;
+                sa.rgb[((size_t)(a.height - 1 - (ty0 + r)) * a.width + tx0) * 3 + c] = s_rgb[(kTileH - 1 - r) * kRgbRow + c];
             }
         }
+        if (tid == 0) sa.rgb_zero[tile] = touched ? 0u : 1u;
+    } else if (SHADE && touched && tid == 0) {
+        sa.rgb_zero[tile] = 0u;
     }
 }
 

@@ -28,6 +28,9 @@ struct ShadeArgs {
     unsigned long long* diag;
     Maps maps;
     int fresh;                      // frame was cleared: pixels not shaded now are written as (0,0,0)
+    // per raster tile: nonzero = the tile's RGB in memory is all zeros already (a cleared frame need not rewrite it)
+    uint32_t* rgb_zero;
+    int rgb_tma;                    // the frame layout allows the TMA tile store (row pitch a multiple of 16 bytes)
 };
 
 // util.rs:34-41 addressing: (uv * size) as u32, image::get_pixel panics when outside -> counted, clamped.

@@ -10,6 +10,7 @@
 #include "k_shade.cuh"
 #include "k_misc.cuh"
 
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstring>
@@ -48,6 +49,11 @@ struct tr_scene {
         uint32_t* tile_state = nullptr;    // per raster tile: 1 = cleared, key memory stale
         uint8_t* rgb = nullptr;
         float* shadow = nullptr;
+        // per raster tile, nonzero = the tile of rgb / shadow holds its cleared value in memory (k_raster skips the store)
+        uint32_t* rgb_zero = nullptr;
+        uint32_t* shadow_clear = nullptr;
+        CUtensorMap rgb_map{};             // rgb as a (width*3 bytes) x height u8 tensor, box = one raster tile
+        bool rgb_tma = false;
         SetupOut cam{}, lit{};
         Bins bins{};
         cudaStream_t stream = nullptr;
@@ -125,12 +131,41 @@ int launch_ok(const char* what) {
     return TR_OK;
 }
 
+// The slot's RGB frame as a 2-D u8 tensor (row = width*3 bytes) whose box is one raster tile: the tile kernel stores
+// its shared-memory tile with one TMA instruction and the hardware clips it at the frame border.  Needs a row pitch
+// that is a multiple of 16 bytes; other widths keep the byte-wise store.  cuTensorMapEncodeTiled comes from the
+// driver through the runtime's entry-point query, so libcuda is not linked.
+int make_rgb_map(tr_scene* s, tr_scene::Slot* sl) {
+    sl->rgb_tma = false;
+    if ((s->width * 3) % 16 != 0) return TR_OK;
+    using EncodeTiled = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                     const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult found;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &found) != cudaSuccess || found != cudaDriverEntryPointSuccess || !fn)
+        return fail(TR_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    const cuuint64_t dims[2] = {(cuuint64_t)s->width * 3, (cuuint64_t)s->height};
+    const cuuint64_t pitch[1] = {(cuuint64_t)s->width * 3};
+    const cuuint32_t box[2] = {(cuuint32_t)kTileW * 3, (cuuint32_t)kTileH};
+    const cuuint32_t step[2] = {1, 1};
+    CUresult r = reinterpret_cast<EncodeTiled>(fn)(&sl->rgb_map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, sl->rgb, dims, pitch, box, step,
+                                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                   CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(TR_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for a %ux%u frame", (int)r, s->width, s->height);
+    sl->rgb_tma = true;
+    return TR_OK;
+}
+
 int fill_state(tr_scene* s, float z_init, bool do_keys, bool do_shadow, bool do_rgb) {
     if (!do_keys && !do_shadow && !do_rgb) return TR_OK;
     Scoped sp(s, KS_CLEAR);
     k_fill_state<<<148 * 8, 256, 0, s->stream>>>(S(s).keys, S(s).shadow, reinterpret_cast<uint32_t*>(S(s).rgb), s->n_px,
                                                  (s->n_px * 3 + 3) / 4, z_init, do_keys, do_shadow, do_rgb);
-    if (do_keys) CU(cudaMemsetAsync(S(s).tile_state, 0, (size_t)s->tiles_x * s->tiles_y * 4, s->stream));
+    const size_t tile_bytes = (size_t)s->tiles_x * s->tiles_y * 4;
+    if (do_keys) CU(cudaMemsetAsync(S(s).tile_state, 0, tile_bytes, s->stream));
+    if (do_rgb) CU(cudaMemsetAsync(S(s).rgb_zero, 1, tile_bytes, s->stream));
+    if (do_shadow) CU(cudaMemsetAsync(S(s).shadow_clear, z_init == -3.402823466e38f ? 1 : 0, tile_bytes, s->stream));
     return launch_ok("k_fill_state");
 }
 
@@ -271,6 +306,11 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
         CU(cudaMalloc(&sl.keys, s->n_px * 8));
         CU(cudaMalloc(&sl.rgb, s->n_px * 3 + 16));
         CU(cudaMalloc(&sl.shadow, s->n_px * 4));
+        CU(cudaMalloc(&sl.rgb_zero, n_tiles * 4));
+        CU(cudaMemset(sl.rgb_zero, 0, n_tiles * 4));
+        CU(cudaMalloc(&sl.shadow_clear, n_tiles * 4));
+        CU(cudaMemset(sl.shadow_clear, 0, n_tiles * 4));
+        if ((rc = make_rgb_map(s, &sl))) return rc;
         CU(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
     }
@@ -304,7 +344,7 @@ void destroy_impl(tr_scene* s) {
     for (auto& sl : s->slots) {
         if (sl.stream) { cudaStreamSynchronize(sl.stream); cudaStreamDestroy(sl.stream); }
         if (sl.done) cudaEventDestroy(sl.done);
-        cudaFree(sl.keys); cudaFree(sl.tile_state); cudaFree(sl.rgb); cudaFree(sl.shadow);
+        cudaFree(sl.keys); cudaFree(sl.tile_state); cudaFree(sl.rgb); cudaFree(sl.shadow); cudaFree(sl.rgb_zero); cudaFree(sl.shadow_clear);
         cudaFree(sl.cam.rec); cudaFree(sl.cam.var); cudaFree(sl.cam.bbox); cudaFree(sl.lit.rec); cudaFree(sl.lit.bbox);
         cudaFree(sl.bins.count); cudaFree(sl.bins.list);
     }
@@ -332,6 +372,7 @@ ShadeArgs shade_args(tr_scene* s, bool fresh_rgb) {
     a.keys = S(s).keys; a.tile_state = S(s).tile_state; a.tiles_x = s->tiles_x;
     a.rec = S(s).cam.rec; a.var = S(s).cam.var; a.shadow = S(s).shadow;
     a.rgb = S(s).rgb; a.ao_accum = s->ao; a.diag = s->diag; a.maps = s->maps; a.fresh = fresh_rgb ? 1 : 0;
+    a.rgb_zero = S(s).rgb_zero; a.rgb_tma = S(s).rgb_tma ? 1 : 0;
     return a;
 }
 
@@ -344,14 +385,14 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     a.bins = S(s).bins;
     a.n_triangles = s->n_tri; a.width = s->width; a.height = s->height; a.tiles_x = s->tiles_x;
     a.epoch = epoch; a.fresh = fresh ? 1 : 0;
-    a.keys = S(s).keys; a.tile_state = S(s).tile_state; a.depth = S(s).shadow; a.diag = s->diag;
+    a.keys = S(s).keys; a.tile_state = S(s).tile_state; a.depth = S(s).shadow; a.depth_clear = S(s).shadow_clear; a.diag = s->diag;
     ShadeArgs sa = shade_args(s, fresh_rgb);
     // centre-out launch order shortens a lone frame's tail; overlapped batches do better in plain row order, where one
     // frame's cheap border tiles run beside the previous frame's heavy ones (measured: profiles/README.md)
     a.tile_order = s->tile_order + (s->overlapping ? (size_t)s->tiles_x * s->tiles_y : 0);
     dim3 grid(s->tiles_x * s->tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
-#define TR_RASTER(M) k_raster<M><<<grid, kRasterThreads, 0, s->stream>>>(a, sa, u)
+#define TR_RASTER(M) k_raster<M><<<grid, kRasterThreads, 0, s->stream>>>(a, sa, u, S(s).rgb_map)
     switch (mode) {
         case kModeDepthOnly: TR_RASTER(kModeDepthOnly); break;
         case kModeVisibility: TR_RASTER(kModeVisibility); break;
