@@ -405,6 +405,12 @@ def run_gpu(args, rank, world, local_rank):
                                              "frac": frame_bytes / (frame_us * 1e-6) / 1e9 / peak},
                             "batch": batch_roofline(ms / args.steps / frames_per_step * 1e3, n_px, covered, n_tri, peak)}
         if world == 1:
+            # what a rasteriser resolving visibility with global 64-bit atomicMin could reach on this box
+            # (distinct addresses, every atomic updates, one atomic per fragment); k_raster resolves in registers instead
+            rate = tr.bench_atomic_min(W4K, H4K, rounds=4, repeats=3, device=dev)
+            line["atomic_min_peak"] = {"atomics_per_s": rate, "equivalent_GB_per_s": rate * 8 / 1e9,
+                                       "us_per_4k_depth_layer": n_px / rate * 1e6,
+                                       "note": "micro-benchmark only (tr_bench_atomic_min); not on the render path"}
             line["cpu_baseline"] = cpu_baseline(model)
     for s in scenes.values():
         s.close()

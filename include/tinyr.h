@@ -137,6 +137,10 @@ int tr_selftest_exact_quotient(int device, uint64_t n_pairs, uint64_t seed, uint
 /* Device self-test of the fragment stage's shared-divisor quotients (k_tile.cuh shared_divisor/quotient: nvcc's own
  * division sequence with the divisor-only part hoisted) against `a / b`; *mismatches must come back 0. */
 int tr_selftest_shared_divisor(int device, uint64_t n_pairs, uint64_t seed, uint64_t* mismatches);
+/* Micro-benchmark: rate of global 64-bit atomicMin on a width x height key plane, distinct
+ * addresses, warp = 8x4 pixel block, `rounds` updating atomics per key; *atomics_per_second is the best of `repeats`
+ * timed launches (CUDA events).  Not on the render path: k_raster resolves visibility in registers. */
+int tr_bench_atomic_min(int device, uint32_t width, uint32_t height, uint32_t rounds, uint32_t repeats, double* atomics_per_second);
 void* tr_host_alloc(size_t bytes);                                                /* pinned host memory for fast get_* copies */
 void tr_host_free(void* p);
 

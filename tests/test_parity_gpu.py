@@ -193,3 +193,11 @@ def test_large_polygons_literal_path(tinyr, oracle):
         assert ((vis == 1200) | (vis == 1201)).sum() > 10 ** 6          # the big polygons do win a large area
         assert st["depth_bits_differ"] == 0
         g.close()
+
+
+def test_atomic_min_microbenchmark_runs(tinyr):
+    """the global 64-bit atomicMin rate is measured on the box (a yardstick, not on the render path)."""
+    rate = tinyr.bench_atomic_min(1024, 512, rounds=2, repeats=2)
+    assert rate > 1e8, rate
+    with pytest.raises(tinyr.TinyrError):
+        tinyr.bench_atomic_min(4, 2)

@@ -81,6 +81,21 @@ __global__ void __launch_bounds__(256) k_selftest_quotient(unsigned long long n,
     if (bad) atomicAdd(mismatches, bad);
 }
 
+// Micro-benchmark for SURVEY.md §8(d): the rate of 64-bit atomicMin on distinct addresses in the pattern a rasteriser
+// that resolves visibility in global memory would produce — each warp owns an 8x4 pixel block of a row-major key
+// plane (8 consecutive keys on 4 rows) and every lane hits its own key `rounds` times with a decreasing value, so every
+// atomic updates.  k_raster resolves winners in registers instead; this number is what that design is measured against.
+__global__ void __launch_bounds__(256) k_bench_atomic_min(unsigned long long* keys, uint32_t width, uint32_t height, uint32_t rounds) {
+    const uint32_t blocks_x = width / 8, blocks_y = height / 4;
+    const uint32_t n_blocks = blocks_x * blocks_y;
+    const uint32_t lane = threadIdx.x & 31u, warps = gridDim.x * (blockDim.x >> 5);
+    for (uint32_t b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); b < n_blocks; b += warps) {
+        const uint32_t px = (b % blocks_x) * 8 + (lane & 7u), py = (b / blocks_x) * 4 + (lane >> 3);
+        unsigned long long* at = keys + (size_t)py * width + px;
+        for (uint32_t r = 0; r < rounds; ++r) atomicMin(at, ((unsigned long long)(0x7fffffffu - r) << 32) | b);
+    }
+}
+
 // Self-test of shared_divisor()/quotient() (k_tile.cuh) against `a / b`: divisors of moderate magnitude, numerators
 // from vanishing to 2^12 times the divisor (what normalisations and homogeneous divides feed it).  Counts results whose
 // bits differ from the division's, ignoring the sign of a zero result.

@@ -24,6 +24,13 @@ def device_count():
     return n.value
 
 
+def bench_atomic_min(width, height, rounds=4, repeats=5, device=0):
+    """Global 64-bit atomicMin rate (atomics/s) on a width x height key plane (SURVEY.md 8(d) micro-benchmark)."""
+    rate = ctypes.c_double(0.0)
+    _check(lib().tr_bench_atomic_min(device, width, height, rounds, repeats, ctypes.byref(rate)))
+    return rate.value
+
+
 def load_obj(path):
     """obj::raw::parse_obj as the reference uses it (app.rs:94): returns positions, uvs, normals, tri_idx."""
     m = _Mesh()
