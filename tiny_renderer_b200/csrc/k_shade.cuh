@@ -65,39 +65,56 @@ struct DiagLocal {
     }
 };
 
+// counter += cond as one predicated add (the compiler's own rendering of `if (c) ++n` is add + predicated undo).
+__device__ __forceinline__ void count_if_ge(uint32_t& n, float a, float b) {
+    asm("{ .reg .pred p; setp.ge.f32 p, %1, %2; @p add.u32 %0, %0, 1; }" : "+r"(n) : "f"(a), "f"(b));
+}
+__device__ __forceinline__ void count_if_geu(uint32_t& n, uint32_t a, uint32_t b) {
+    asm("{ .reg .pred p; setp.hs.u32 p, %1, %2; @p add.u32 %0, %0, 1; }" : "+r"(n) : "r"(a), "r"(b));
+}
+__device__ __forceinline__ void count_if_zero(uint32_t& n, float w) {       // w == 0.0 (either sign; NaN does not count)
+    asm("{ .reg .pred p; setp.eq.f32 p, %1, 0f00000000; @p add.u32 %0, %0, 1; }" : "+r"(n) : "f"(w));
+}
+
 // `f32::round() as u32` (shader.rs:774-775): round half away from zero, then Rust's saturating cast (negative and
 // NaN -> 0).  t = trunc(x) and x - t are exact, so this equals cast_u32(roundf(x)) for every input.
 __device__ __forceinline__ uint32_t round_u32(float x) {
     float t = truncf(x);
     uint32_t r = __float2uint_rz(t);
-    if (x - t >= 0.5f) r += 1u;
+    count_if_ge(r, x - t, 0.5f);
     return r;
 }
 
 // Shadow-buffer lookup of shader.rs:774-778 / 909-912 / 932-935: round, saturating cast, wrapping u32 index.
 __device__ __forceinline__ float shadow_lookup(const float* shadow, f3 s, uint32_t width, uint32_t n_px, DiagLocal& dl) {
     uint32_t sx = round_u32(s.x), sy = round_u32(s.y);
-    dl.xwrap += sx >= width ? 1u : 0u;
+    count_if_geu(dl.xwrap, sx, width);
     uint32_t idx = sx + sy * width;
-    if (idx >= n_px) { dl.oob += 1u; return -3.402823466e38f; }
-    return __ldg(&shadow[idx]);
+    count_if_geu(dl.oob, idx, n_px);
+    return idx >= n_px ? -3.402823466e38f : __ldg(&shadow[idx]);
 }
 
+#ifndef TR_AO_UNROLL
+#define TR_AO_UNROLL 4
+#endif
+constexpr int kAoUnroll = TR_AO_UNROLL;
 // Occlusion fragment (shader.rs:886-947) for a pixel whose depth z and world position wp = from_homogeneous(i_vpmv *
 // (px, py, z, 1)) are known; returns the gray level.
 __device__ __forceinline__ uint32_t occlusion_gray(const float* shadow, const Uniforms& u, int px, int py, float z, f3 wp, DiagLocal& dl) {
     const uint32_t n_px = u.width * u.height;
     bool ok;
-    f3 fs = dehomog_shared(xform(u.shadow_from_screen, f4{(float)px, (float)py, z, 1.0f}), ok);
-    dl.w_zero += ok ? 0u : 1u;
+    const f4 fh = xform(u.shadow_from_screen, f4{(float)px, (float)py, z, 1.0f});
+    f3 fs = dehomog_shared(fh, ok);
+    count_if_zero(dl.w_zero, fh.w);
     float fsv = shadow_lookup(shadow, fs, u.width, n_px, dl);
     float occ = 1.0f;
     const SharedDivisor d20 = shared_divisor(20.0f);        // (sv - fsv) / 20.0 below: numerators in (1, ~300)
-#pragma unroll 4
+#pragma unroll kAoUnroll
     for (int k = 0; k < 16; ++k) {
         f3 sp = wp + u.ao_step[k];
-        f3 sc = dehomog_shared(xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f}), ok);
-        dl.w_zero += ok ? 0u : 1u;
+        const f4 sh = xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f});
+        f3 sc = dehomog_shared(sh, ok);
+        count_if_zero(dl.w_zero, sh.w);
         float sv = shadow_lookup(shadow, sc, u.width, n_px, dl);
         if (sv - 1.0f > fsv) {
             float strength = fminf(quotient(sv - fsv, d20), 1.0f);
