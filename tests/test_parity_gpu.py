@@ -201,3 +201,12 @@ def test_atomic_min_microbenchmark_runs(tinyr):
     assert rate > 1e8, rate
     with pytest.raises(tinyr.TinyrError):
         tinyr.bench_atomic_min(4, 2)
+
+
+def test_round_u32_selftest(tinyr):
+    """Shadow-lookup rounding (`f32::round() as u32`, shader.rs:774-775) in its two-instruction form against the
+    literal one on every f32 bit pattern."""
+    import ctypes
+    bad = ctypes.c_uint64(123)
+    rc = tinyr.lib().tr_selftest_round_u32(0, ctypes.byref(bad))
+    assert rc == 0 and bad.value == 0, (rc, bad.value)

@@ -81,6 +81,17 @@ __global__ void __launch_bounds__(256) k_selftest_quotient(unsigned long long n,
     if (bad) atomicAdd(mismatches, bad);
 }
 
+// Self-test of round_u32() (k_shade.cuh) against the literal `f32::round() as u32` on every f32 bit pattern.
+__global__ void __launch_bounds__(256) k_selftest_round_u32(unsigned long long* mismatches) {
+    const unsigned long long i0 = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x, stride = (unsigned long long)gridDim.x * blockDim.x;
+    unsigned long long bad = 0;
+    for (unsigned long long i = i0; i < (1ull << 32); i += stride) {
+        const float x = __uint_as_float((uint32_t)i);
+        bad += round_u32(x) == round_u32_literal(x) ? 0ull : 1ull;
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
+
 // Micro-benchmark for SURVEY.md §8(d): the rate of 64-bit atomicMin on distinct addresses in the pattern a rasteriser
 // that resolves visibility in global memory would produce — each warp owns an 8x4 pixel block of a row-major key
 // plane (8 consecutive keys on 4 rows) and every lane hits its own key `rounds` times with a decreasing value, so every

@@ -77,12 +77,16 @@ __device__ __forceinline__ void count_if_zero(uint32_t& n, float w) {       // w
 }
 
 // `f32::round() as u32` (shader.rs:774-775): round half away from zero, then Rust's saturating cast (negative and
-// NaN -> 0).  t = trunc(x) and x - t are exact, so this equals cast_u32(roundf(x)) for every input.
-__device__ __forceinline__ uint32_t round_u32(float x) {
-    float t = truncf(x);
-    uint32_t r = __float2uint_rz(t);
-    count_if_ge(r, x - t, 0.5f);
-    return r;
+// NaN -> 0, >= 2^32 -> u32::MAX).  For x >= 0 that is floor(x + 0.5); the sum is formed rounding toward zero, so it
+// never reaches the next integer n unless x + 0.5 >= n exactly (n < 2^24 is representable; above 2^23 x is an integer
+// and the sum truncates back to x), and the truncating, saturating conversion finishes the job.  For x < 0 both sides
+// give 0 (x + 0.5 < 0.5 truncates to 0 or saturates).  tr_selftest_round_u32 checks all 2^32 bit patterns on device.
+__device__ __forceinline__ uint32_t round_u32(float x) { return __float2uint_rz(__fadd_rz(x, 0.5f)); }
+// The literal form, kept for the self-test.
+__device__ __forceinline__ uint32_t round_u32_literal(float x) {
+    const float r = roundf(x);
+    if (r != r || r <= 0.0f) return 0u;
+    return r >= 4294967296.0f ? 0xffffffffu : (uint32_t)r;
 }
 
 // Shadow-buffer lookup of shader.rs:774-778 / 909-912 / 932-935: round, saturating cast, wrapping u32 index.
