@@ -121,7 +121,10 @@ __device__ __forceinline__ void stage_polygon(const RasterArgs& a, uint32_t t, i
     uint32_t blocks = bbox_block_mask(max(bb.x, tx0) - tx0, max(bb.y, ty0) - ty0, min(bb.z, tx1) - tx0, min(bb.w, ty1) - ty0);
     uint32_t id = t;
     bool exact = true;
-    if (ex <= kExactExtent && ey <= kExactExtent) {
+    // (non-finite vertex depths also take the literal path: the exact sweep then needs no NaN test per fragment,
+    // because barycentrics in [0, 1] times finite depths cannot produce one)
+    const bool finite_z = fabsf(r1.z) <= 3.402823466e38f && fabsf(r1.w) <= 3.402823466e38f && fabsf(r2.x) <= 3.402823466e38f;
+    if (ex <= kExactExtent && ey <= kExactExtent && finite_z) {
         int ux = x1 - x0, uy = x2 - x0, vx = y1 - y0, vy = y2 - y0;
         int cz = ux * vy - uy * vx;
         int s = cz < 0 ? -1 : 1;
@@ -313,7 +316,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
                                 if (!fragment_depth(e.x, e.y, e.z, e.w, f.x, f.y, __int_as_float(g.x), __int_as_float(g.y), __int_as_float(g.z),
                                                     px, py + 4 * k, z, b0, b1, b2)) continue;
                             }
-                            if (z != z) { atomicAdd(&a.diag[D_NAN_DEPTH], 1ull); continue; }
+                            if (!EXACT && z != z) { atomicAdd(&a.diag[D_NAN_DEPTH], 1ull); continue; }
                             if (DEPTH_ONLY) {
                                 if (z >= bz[k]) bz[k] = z;                               // shader.rs:703
                             } else if (z > bz[k] || (z == bz[k] && lo < blo[k] && blo[k] != kNoTri)) {
