@@ -276,10 +276,37 @@ def run_ao(args, rank, world, dev, model, dist, stream):
                       "3840x2160, camera angle 0" % (AO_LIGHTS, drawn)}
 
 
+def bind_to_gpu_numa_node(dev):
+    """Pin this rank's host threads (and with them the pinned frame buffers it allocates next) to the NUMA node the GPU
+    hangs off, so that N ranks copying frames to the host do not all cross one socket.  Best effort: returns the
+    node or None when the box does not expose the topology."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(dev).pci_bus_id
+        dom = torch.cuda.get_device_properties(dev).pci_domain_id
+        devid = torch.cuda.get_device_properties(dev).pci_device_id
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bus, devid)
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except Exception:
+        return None
+
+
 def run_gpu(args, rank, world, local_rank):
     import torch
     import tiny_renderer_b200 as tr
     from tiny_renderer_b200.scene import Scene
+    numa_node = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -364,7 +391,8 @@ def run_gpu(args, rank, world, local_rank):
                     "d2h_bytes_per_step": frames_per_step * n_px * 3,
                     "note": "tr_scene_render_views(views, frames -> pinned host): per frame clear/set_light_direction/set_camera/"
                             "render + device->host copy of the RGB8 frame, all inside the timed region; inputs are the 12 "
-                            "floats of camera+light per frame (kernel arguments); PCIe-bound: 24.9 MB per frame"},
+                            "floats of camera+light per frame (kernel arguments); PCIe-bound: 24.9 MB per frame",
+                    "host_numa_node": numa_node},
             "gpu_launches": int(launches), "clocks": clocks}
 
     if rank == 0:

@@ -32,9 +32,12 @@ namespace tr {
 #ifdef TR_MIN_CTAS
 #define TR_RASTER_BOUNDS __launch_bounds__(kRasterThreads, TR_MIN_CTAS)
 #else
-// the compiler's own register choice measured best, except for the darboux instantiation, which lands at 65
-// registers (3 CTAs per SM) unless held to 4 CTAs per SM (A/B in profiles/README.md)
-#define TR_RASTER_BOUNDS __launch_bounds__(kRasterThreads, MODE == P_DARBOUX ? 4 : 0)
+// Residency measured best (A/B in profiles/README.md): 6 CTAs per SM (40 registers, no spills; also the shared-memory
+// limit) for every instantiation but darboux, whose fragment code spills below 64 registers and is held to 4.
+#ifndef TR_MIN_CTAS_LIGHT
+#define TR_MIN_CTAS_LIGHT 6
+#endif
+#define TR_RASTER_BOUNDS __launch_bounds__(kRasterThreads, MODE == P_DARBOUX ? 4 : TR_MIN_CTAS_LIGHT)
 #endif
 #ifndef TR_PIXELS_PER_LANE
 #define TR_PIXELS_PER_LANE 2
