@@ -37,7 +37,10 @@ namespace tr {
 #ifndef TR_MIN_CTAS_LIGHT
 #define TR_MIN_CTAS_LIGHT 6
 #endif
-#define TR_RASTER_BOUNDS __launch_bounds__(kRasterThreads, MODE == P_DARBOUX ? 4 : TR_MIN_CTAS_LIGHT)
+#ifndef TR_MIN_CTAS_DARBOUX
+#define TR_MIN_CTAS_DARBOUX 4
+#endif
+#define TR_RASTER_BOUNDS __launch_bounds__(kRasterThreads, MODE == P_DARBOUX ? TR_MIN_CTAS_DARBOUX : TR_MIN_CTAS_LIGHT)
 #endif
 #ifndef TR_PIXELS_PER_LANE
 #define TR_PIXELS_PER_LANE 2
