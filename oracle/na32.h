@@ -14,6 +14,14 @@
 //   * Rotation3::rotation_between / from_axis_angle (geometry/rotation_specialization.rs)
 // PARITY STATUS vs the real Rust binary: UNPINNED (no Rust toolchain, no goldens in the reference).
 // Compile with -ffp-contract=off and never with -ffast-math: every * and + below is one IEEE-754 op.
+//
+// Sensitivity switches (tools/oracle_sensitivity.py only; never defined in the oracle the tests use): because the
+// orders above are a restatement, the tool rebuilds the oracle with a different but equally plausible order for one
+// primitive at a time and counts how many output pixels move, which bounds what "unpinned" can cost.
+//   NA32_ALT_GEMV_PAIRWISE   4-dim mat*vec rows summed (t0 + t2) + (t1 + t3) (the dot4 association) instead of axpy order
+//   NA32_ALT_DOT3_RIGHT      3-dim dot as p + (q + r)
+//   NA32_ALT_NORMALIZE_RECIP normalize multiplies by 1/norm instead of dividing each component
+//   NA32_ALT_INV4_DIVIDE     4x4 inverse divides every cofactor by det instead of multiplying by 1/det
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -36,7 +44,11 @@ inline V3 unscale(V3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
 
 inline float dot(V3 a, V3 b) {
     float p = a.x * b.x, q = a.y * b.y, r = a.z * b.z;
+#ifdef NA32_ALT_DOT3_RIGHT
+    return p + (q + r);
+#else
     return (p + q) + r;
+#endif
 }
 inline float dot(V4 a, V4 b) {
     float p = a.x * b.x, q = a.y * b.y, r = a.z * b.z, s = a.w * b.w;
@@ -48,12 +60,23 @@ inline V3 cross(V3 a, V3 b) {
 }
 inline float norm_squared(V3 a) { return 0.0f + dot(a, a); }
 inline float norm(V3 a) { return std::sqrt(norm_squared(a)); }
+#ifdef NA32_ALT_NORMALIZE_RECIP
+inline V3 normalize(V3 a) { return scale(a, 1.0f / norm(a)); }
+#else
 inline V3 normalize(V3 a) { return unscale(a, norm(a)); }
+#endif
 
 // gemv, column-axpy order.
 inline V4 mul(const M4& a, V4 x) {
     float xs[4] = {x.x, x.y, x.z, x.w};
     float y[4];
+#ifdef NA32_ALT_GEMV_PAIRWISE
+    for (int i = 0; i < 4; ++i) {
+        float t0 = a.at(i, 0) * xs[0], t1 = a.at(i, 1) * xs[1], t2 = a.at(i, 2) * xs[2], t3 = a.at(i, 3) * xs[3];
+        y[i] = (t0 + t2) + (t1 + t3);
+    }
+    return {y[0], y[1], y[2], y[3]};
+#endif
     for (int i = 0; i < 4; ++i) y[i] = a.at(i, 0) * xs[0];
     for (int j = 1; j < 4; ++j)
         for (int i = 0; i < 4; ++i) y[i] = a.at(i, j) * xs[j] + y[i];
@@ -160,6 +183,10 @@ inline bool try_inverse(const M4& a, M4* out) {
     inv[15] =  m[0]*m[5]*m[10]  - m[0]*m[6]*m[9]   - m[4]*m[1]*m[10] + m[4]*m[2]*m[9]  + m[8]*m[1]*m[6]   - m[8]*m[2]*m[5];
     float det = m[0]*inv[0] + m[1]*inv[4] + m[2]*inv[8] + m[3]*inv[12];
     if (det == 0.0f) return false;
+#ifdef NA32_ALT_INV4_DIVIDE
+    for (int k = 0; k < 16; ++k) out->m[k] = inv[k] / det;
+    return true;
+#endif
     float inv_det = 1.0f / det;
     for (int k = 0; k < 16; ++k) out->m[k] = inv[k] * inv_det;
     return true;

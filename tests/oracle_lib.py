@@ -27,7 +27,8 @@ def build_oracle():
 def lib():
     global _LIB
     if _LIB is None:
-        path = os.path.join(_ORACLE_DIR, "liboracle.so")
+        # TINYR_ORACLE_LIB: an alternative build of the oracle (tools/oracle_sensitivity.py)
+        path = os.environ.get("TINYR_ORACLE_LIB") or os.path.join(_ORACLE_DIR, "liboracle.so")
         if not os.path.exists(path):
             build_oracle()
         L = ctypes.CDLL(path)
