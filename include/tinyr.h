@@ -140,6 +140,10 @@ int tr_selftest_shared_divisor(int device, uint64_t n_pairs, uint64_t seed, uint
 /* Device self-test of the shadow-lookup rounding (k_shade.cuh round_u32: `f32::round() as u32`, shader.rs:774-775)
  * against its literal form on all 2^32 f32 bit patterns; *mismatches must come back 0. */
 int tr_selftest_round_u32(int device, uint64_t* mismatches);
+/* Device self-test of the normalisations' square root (k_tile.cuh sqrt_fast_path: nvcc's own IEEE sqrt fast path,
+ * spelled out to share its range test with the division that follows) against sqrtf() on every f32 bit pattern it
+ * accepts; *mismatches must come back 0, *accepted is the number of patterns tested (about 1.9 * 2^30). */
+int tr_selftest_sqrt(int device, uint64_t* mismatches, uint64_t* accepted);
 /* Micro-benchmark: rate of global 64-bit atomicMin on a width x height key plane, distinct
  * addresses, warp = 8x4 pixel block, `rounds` updating atomics per key; *atomics_per_second is the best of `repeats`
  * timed launches (CUDA events).  Not on the render path: k_raster resolves visibility in registers. */

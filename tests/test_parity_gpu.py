@@ -210,3 +210,13 @@ def test_round_u32_selftest(tinyr):
     bad = ctypes.c_uint64(123)
     rc = tinyr.lib().tr_selftest_round_u32(0, ctypes.byref(bad))
     assert rc == 0 and bad.value == 0, (rc, bad.value)
+
+
+def test_sqrt_fast_path_selftest(tinyr):
+    """The normalisations' square root (nvcc's IEEE sqrt fast path spelled out, k_tile.cuh) against sqrtf() on every
+    f32 bit pattern inside its range test."""
+    import ctypes
+    bad, n = ctypes.c_uint64(123), ctypes.c_uint64(0)
+    rc = tinyr.lib().tr_selftest_sqrt(0, ctypes.byref(bad), ctypes.byref(n))
+    assert rc == 0 and bad.value == 0, (rc, bad.value)
+    assert n.value == 0x72800000, hex(n.value)           # every pattern the range test accepts was compared

@@ -81,6 +81,22 @@ __global__ void __launch_bounds__(256) k_selftest_quotient(unsigned long long n,
     if (bad) atomicAdd(mismatches, bad);
 }
 
+// Self-test of sqrt_fast_path() (k_tile.cuh) against sqrtf() on every f32 bit pattern it accepts.
+__global__ void __launch_bounds__(256) k_selftest_sqrt(unsigned long long* mismatches, unsigned long long* accepted) {
+    const unsigned long long i0 = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x, stride = (unsigned long long)gridDim.x * blockDim.x;
+    unsigned long long bad = 0, n_ok = 0;
+    for (unsigned long long i = i0; i < (1ull << 32); i += stride) {
+        const float x = __uint_as_float((uint32_t)i);
+        bool ok;
+        const float s = sqrt_fast_path(x, ok);
+        if (!ok) continue;
+        ++n_ok;
+        bad += __float_as_uint(s) == __float_as_uint(sqrtf(x)) ? 0ull : 1ull;
+    }
+    if (bad) atomicAdd(mismatches, bad);
+    atomicAdd(accepted, n_ok);
+}
+
 // Self-test of round_u32() (k_shade.cuh) against the literal `f32::round() as u32` on every f32 bit pattern.
 __global__ void __launch_bounds__(256) k_selftest_round_u32(unsigned long long* mismatches) {
     const unsigned long long i0 = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x, stride = (unsigned long long)gridDim.x * blockDim.x;
