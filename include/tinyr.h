@@ -124,7 +124,10 @@ int tr_ao_generate_lights(const float* positions_xyz, uint32_t n_positions, cons
 /* ---- device plumbing -------------------------------------------------------------------------------- */
 int tr_device_count(int* n);
 int tr_scene_set_stream(tr_scene* s, void* cuda_stream);                          /* run on the caller's cudaStream_t (NULL = scene's own) */
-int tr_scene_device_frame(tr_scene* s, void** device_ptr_rgb8_topdown);           /* zero-copy access for tests / interop */
+int tr_scene_device_frame(tr_scene* s, void** device_ptr_rgb8_topdown);
+/* Test hook: bit 0 makes the occlusion samples always take the range-tested division (k_shade.cuh occlusion_gray picks
+ * between two forms of the same arithmetic per pixel; results must not depend on the choice). */
+int tr_scene_set_debug_flags(tr_scene* s, uint32_t flags);           /* zero-copy access for tests / interop */
 int tr_scene_timer_begin(tr_scene* s);                                            /* CUDA event on the scene stream */
 int tr_scene_timer_end(tr_scene* s, float* elapsed_ms);                           /* records + synchronises */
 /* Per-kernel device times (CUDA events around every launch while enabled).  names: K1 vertex_setup, K2 bin,

@@ -196,3 +196,27 @@ def test_config5_8k_full_pixel_parity_sample(tinyr, oracle, asset):
     assert np.array_equal(vis_last, o.raw_visibility())          # visibility of the last view, bit-exact
     assert o.diagnostics()["texel_oob"] == 0
     g.close()
+
+
+def test_occlusion_division_forms_agree(tinyr):
+    """occlusion_gray picks per pixel between a sample loop with and without the division's range test (the hoisted
+    bound in k_shade.cuh); both are the same arithmetic, so forcing the tested form must not change a single sum —
+    neither in the many-light batch (K6) nor in the fused single-light pipeline."""
+    from tiny_renderer_b200.scene import Scene
+    model = get_model("diablo")
+    w, h = 416, 304
+    lights, _ = tinyr.generate_ao_lights(model.positions, 12)
+    lf, la, up, _ = assets.view_vectors(0.4, 0.0)
+    sums, frames = [], []
+    for flags in (0, 1):
+        s = Scene(w, h, model, "occlusion", ring=2)
+        s.set_debug_flags(flags)
+        s.set_camera(lf, la, up)
+        sums.append(s.render_ao(lights).copy())
+        s.clear(); s.set_light_direction(lights[3]); s.render()
+        frames.append(s.get_frame_buffer().copy())
+        assert s.diagnostics()["w_zero"] == 0
+        s.close()
+    assert sums[0].sum() > 0
+    assert np.array_equal(sums[0], sums[1])
+    assert np.array_equal(frames[0], frames[1])

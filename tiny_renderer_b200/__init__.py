@@ -102,6 +102,7 @@ def lib():
             "tr_write_tga": [ctypes.c_char_p, vp, u32, u32, i32],
             "tr_scene_create_from_dir": [ctypes.POINTER(vp), ctypes.c_char_p, ctypes.c_char_p, u32, u32, ctypes.c_int32, u32],
             "tr_selftest_shared_divisor": [ctypes.c_int, ctypes.c_uint64, ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)],
+            "tr_scene_set_debug_flags": [vp, u32],
             "tr_selftest_sqrt": [ctypes.c_int, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)],
             "tr_selftest_round_u32": [ctypes.c_int, ctypes.POINTER(ctypes.c_uint64)],
             "tr_bench_atomic_min": [ctypes.c_int, u32, u32, u32, u32, ctypes.POINTER(ctypes.c_double)],

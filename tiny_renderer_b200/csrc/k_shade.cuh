@@ -6,6 +6,7 @@
 // :597-655 darboux, :749-788 shadow, :872-947 occlusion), the samplers of /root/reference/src/scene/util.rs:34-83
 // and color_blend (util.rs:7-13).
 #pragma once
+#include <type_traits>
 #include <cuda_runtime.h>
 #include "k_tile.cuh"
 
@@ -113,18 +114,40 @@ __device__ __forceinline__ uint32_t occlusion_gray(const float* shadow, const Un
     float fsv = shadow_lookup(shadow, fs, u.width, n_px, dl);
     float occ = 1.0f;
     const SharedDivisor d20 = shared_divisor(20.0f);        // (sv - fsv) / 20.0 below: numerators in (1, ~300)
+    // The 16 sample points lie within 0.02 of wp, so their homogeneous w = W(p) (fourth row of u.shadow) lies within
+    // `reach` of W(wp): |row . (p - wp)| <= rowsum * 0.0203 (0.02-long steps, plus the rounding of wp + step for
+    // |wp| <= 1024) and each computed W carries at most 2^-21 * T of rounding error (T bounds the terms' magnitudes).
+    // When reach <= |W(wp)| / 2 and |W(wp)| is in [2^-60, 2^60], every sample's w is in [2^-61, 2^61): non-zero and inside
+    // the shared divisor's range, so the loop needs neither the range test nor the w == 0 count per sample.  The
+    // test only selects between two forms of the same arithmetic (u.debug_flags bit 0 forces the tested form).
+    const float* sm = u.shadow.m;
+    const float reach_a = fmaxf(fmaxf(fabsf(wp.x), fabsf(wp.y)), fabsf(wp.z));
+    const float w_base = fabsf(((sm[12] * wp.x + sm[13] * wp.y) + sm[14] * wp.z) + sm[15]);
+    const float reach = 0.0204f * u.ao_w_rowsum + 0x1p-20f * (u.ao_w_rowsum * (reach_a + 0.03f) + fabsf(sm[15]));
+    const bool untested = reach_a <= 1024.0f && w_base >= 0x1p-60f && w_base <= 0x1p60f && reach <= 0.5f * w_base &&
+                          (u.debug_flags & 1u) == 0u;
+    auto samples = [&](auto untested_c) {
+        constexpr bool UNTESTED = decltype(untested_c)::value;
 #pragma unroll kAoUnroll
-    for (int k = 0; k < 16; ++k) {
-        f3 sp = wp + u.ao_step[k];
-        const f4 sh = xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f});
-        f3 sc = dehomog_shared(sh, ok);
-        count_if_zero(dl.w_zero, sh.w);
-        float sv = shadow_lookup(shadow, sc, u.width, n_px, dl);
-        if (sv - 1.0f > fsv) {
-            float strength = fminf(quotient(sv - fsv, d20), 1.0f);
-            occ -= 0.0625f * strength;
+        for (int k = 0; k < 16; ++k) {
+            f3 sp = wp + u.ao_step[k];
+            const f4 sh = xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f});
+            f3 sc;
+            if (UNTESTED) {
+                const SharedDivisor d = shared_divisor(sh.w);
+                sc = {quotient(sh.x, d), quotient(sh.y, d), 0.0f};          // z of the sample is not used
+            } else {
+                sc = dehomog_shared(sh, ok);
+                count_if_zero(dl.w_zero, sh.w);
+            }
+            float sv = shadow_lookup(shadow, sc, u.width, n_px, dl);
+            if (sv - 1.0f > fsv) {
+                float strength = fminf(quotient(sv - fsv, d20), 1.0f);
+                occ -= 0.0625f * strength;
+            }
         }
-    }
+    };
+    if (untested) samples(std::true_type{}); else samples(std::false_type{});
     return cast_u8(occ * 255.0f + (1.0f - occ) * 0.0f);
 }
 

@@ -65,6 +65,7 @@ struct tr_scene {
     // distance from the screen centre, [1] plain row order
     uint32_t* tile_order = nullptr;
     bool overlapping = false;            // a batch is running frames / light passes concurrently on the slot streams
+    uint32_t debug_flags = 0;            // tr_scene_set_debug_flags -> Uniforms::debug_flags
     uint32_t* ao = nullptr;
     AoList ao_list{};                  // covered pixels of the camera view (many-light AO batch), allocated on first use
     uint32_t ao_list_n = 0;
@@ -458,6 +459,7 @@ int render_impl(tr_scene* s) {
     } else {
         if ((rc = prep_error(prepare_camera(u, s->width, s->height, s->light, s->from, s->at, s->up)))) return rc;
     }
+    u.debug_flags = s->debug_flags;
     if ((rc = run_setup(s, u, false))) return rc;
     if ((rc = run_raster(s, s->pipeline, s->epoch, s->fresh_keys, u, s->fresh_rgb))) return rc;
     s->fresh_keys = false;
@@ -637,6 +639,12 @@ int tr_scene_get_uniforms(tr_scene* s, float out[102]) {
     for (int k = 0; k < 6; ++k) memcpy(out + 16 * k, ms[k]->m, 64);
     out[96] = s->uni.camera_direction.x; out[97] = s->uni.camera_direction.y; out[98] = s->uni.camera_direction.z;
     out[99] = s->uni.t_light.x; out[100] = s->uni.t_light.y; out[101] = s->uni.t_light.z;
+    return TR_OK;
+}
+
+int tr_scene_set_debug_flags(tr_scene* s, uint32_t flags) {
+    NEED(s);
+    s->debug_flags = flags;
     return TR_OK;
 }
 

@@ -154,6 +154,10 @@ class Scene:
 
     __del__ = close
 
+    def set_debug_flags(self, flags):
+        """Test hook (tr_scene_set_debug_flags): bit 0 = occlusion samples always use the range-tested division."""
+        _check(lib().tr_scene_set_debug_flags(self._h, int(flags)))
+
     # ---- reference surface ----
     def clear(self):
         _check(lib().tr_scene_clear(self._h))
