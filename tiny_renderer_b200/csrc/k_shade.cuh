@@ -96,7 +96,7 @@ __device__ __forceinline__ float shadow_lookup(const float* shadow, f3 s, uint32
     count_if_geu(dl.xwrap, sx, width);
     uint32_t idx = sx + sy * width;
     count_if_geu(dl.oob, idx, n_px);
-    return idx >= n_px ? -3.402823466e38f : __ldg(&shadow[idx]);
+    return __ldg(&shadow[min(idx, n_px)]);      // shadow[n_px] is a sentinel holding the cleared value (f32::MIN)
 }
 
 #ifndef TR_AO_UNROLL

@@ -306,7 +306,11 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
         CU(cudaMemset(sl.tile_state, 0, n_tiles * 4));
         CU(cudaMalloc(&sl.keys, s->n_px * 8));
         CU(cudaMalloc(&sl.rgb, s->n_px * 3 + 16));
-        CU(cudaMalloc(&sl.shadow, s->n_px * 4));
+        CU(cudaMalloc(&sl.shadow, (s->n_px + 1) * 4));            // + the sentinel out-of-range lookups read (k_shade.cuh)
+        {
+            const float cleared = -3.402823466e38f;
+            CU(cudaMemcpy(sl.shadow + s->n_px, &cleared, 4, cudaMemcpyHostToDevice));
+        }
         CU(cudaMalloc(&sl.rgb_zero, n_tiles * 4));
         CU(cudaMemset(sl.rgb_zero, 0, n_tiles * 4));
         CU(cudaMalloc(&sl.shadow_clear, n_tiles * 4));
