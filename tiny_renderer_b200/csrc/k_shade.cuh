@@ -215,19 +215,26 @@ __device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Unifor
         float det = m11 * mi1 - m12 * mi2 + m13 * mi3;
         if (det == 0.0f) { atomicAdd(&a.diag[D_SINGULAR_BASIS], 1ull); return 0u; }
         // every entry of the adjugate divided by det (nalgebra 3x3 try_inverse), one shared divisor
-        const float c12 = m13 * m32 - m33 * m12, c13 = m12 * m23 - m22 * m13, c22 = m11 * m33 - m31 * m13,
-                    c23 = m13 * m21 - m23 * m11, c32 = m12 * m31 - m32 * m11, c33 = m11 * m22 - m21 * m12;
-        mat3 I;
-        if (in_fast_division_range(det)) {
-            const SharedDivisor d = shared_divisor(det);
-            I = {{quotient(mi1, d), quotient(c12, d), quotient(c13, d), quotient(-mi2, d), quotient(c22, d), quotient(c23, d),
-                  quotient(mi3, d), quotient(c32, d), quotient(c33, d)}};
-        } else {
-            I = {{mi1 / det, c12 / det, c13 / det, -mi2 / det, c22 / det, c23 / det, mi3 / det, c32 / det, c33 / det}};
-        }
+        const float c12 = m13 * m32 - m33 * m12, c22 = m11 * m33 - m31 * m13, c32 = m12 * m31 - m32 * m11;
         // uvs: r2.z r2.w r3.x = u0 u1 u2 ; r3.y r3.z r3.w = v0 v1 v2
-        f3 lx = unit3_shared(xform(I, f3{r2.w - r2.z, r3.x - r2.z, 0.0f}));
-        f3 ly = unit3_shared(xform(I, f3{r3.z - r3.y, r3.w - r3.y, 0.0f}));
+        const f3 du{r2.w - r2.z, r3.x - r2.z, 0.0f}, dv{r3.z - r3.y, r3.w - r3.y, 0.0f};
+        f3 lx, ly;
+        if (in_fast_division_range(det)) {
+            // The third column of the inverse only ever meets the zero component of du / dv.  On this branch det is
+            // finite and normal, hence so are the cofactors (products of unit-vector components): 0 * I(.,2) is a zero
+            // whose only possible trace is the sign of a zero sum, which no later step can turn into a different
+            // colour (it reaches the result through x / len, products and sums only).  So the column is not formed.
+            const SharedDivisor d = shared_divisor(det);
+            const float i00 = quotient(mi1, d), i01 = quotient(c12, d), i10 = quotient(-mi2, d), i11 = quotient(c22, d),
+                        i20 = quotient(mi3, d), i21 = quotient(c32, d);
+            lx = unit3_shared(f3{i01 * du.y + i00 * du.x, i11 * du.y + i10 * du.x, i21 * du.y + i20 * du.x});
+            ly = unit3_shared(f3{i01 * dv.y + i00 * dv.x, i11 * dv.y + i10 * dv.x, i21 * dv.y + i20 * dv.x});
+        } else {
+            const float c13 = m12 * m23 - m22 * m13, c23 = m13 * m21 - m23 * m11, c33 = m11 * m22 - m21 * m12;
+            const mat3 I = {{mi1 / det, c12 / det, c13 / det, -mi2 / det, c22 / det, c23 / det, mi3 / det, c32 / det, c33 / det}};
+            lx = unit3_shared(xform(I, du));
+            ly = unit3_shared(xform(I, dv));
+        }
         f3 lz = unit3_shared(local_z);
         mat3 B = {{lx.x, ly.x, lz.x, lx.y, ly.y, lz.y, lx.z, ly.z, lz.z}};
         f3 n = unit3_shared(xform(B, nt));
