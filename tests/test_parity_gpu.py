@@ -220,3 +220,49 @@ def test_sqrt_fast_path_selftest(tinyr):
     rc = tinyr.lib().tr_selftest_sqrt(0, ctypes.byref(bad), ctypes.byref(n))
     assert rc == 0 and bad.value == 0, (rc, bad.value)
     assert n.value == 0x72800000, hex(n.value)           # every pattern the range test accepts was compared
+
+
+@pytest.mark.parametrize("pipeline", PIPELINES)
+def test_fuzz_cameras_partly_off_screen(tinyr, oracle, pipeline):
+    """Random cameras, look-at offsets, up vectors and lights (seeded): the model is cut by the frame border, vertices
+    land off screen, bounding boxes are clamped, shadow lookups leave the light's frame.  Everything — visibility,
+    depth, shadow buffer, colours and the counts of the events on which the reference would panic — must equal the
+    oracle's; views the reference cannot prepare must be refused with the same status."""
+    from tiny_renderer_b200.scene import Scene
+    rng = np.random.default_rng(20260 + PIPELINES.index(pipeline))
+    w, h = 336, 250
+    done = 0
+    for trial in range(10):
+        model = get_model("diablo" if trial % 2 else "african_head")
+        d = rng.normal(size=3)
+        d /= np.linalg.norm(d)
+        lf = (d * rng.uniform(0.45, 2.5)).astype(np.float32)
+        la = (rng.uniform(-0.6, 0.6, 3) * (trial % 3 != 0)).astype(np.float32)
+        up = np.array([rng.uniform(-0.3, 0.3), 1.0, rng.uniform(-0.3, 0.3)], np.float32)
+        l = rng.normal(size=3)
+        light = (l / np.linalg.norm(l)).astype(np.float32)
+        g = Scene(w, h, model, pipeline)
+        o = oracle.OracleScene(w, h, model, pipeline)
+        o.clear(); o.set_light_direction(light); o.set_camera(lf, la, up)
+        if o.render(allow_panic=True):
+            with pytest.raises(tinyr.TinyrError) as e:
+                parity.drive(g, lf, la, up, light)
+            assert e.value.name == "TR_ERR_REFERENCE_UNDEFINED", (trial, e.value)
+            g.close()
+            continue
+        parity.drive(g, lf, la, up, light)
+        st = parity.compare(g, o, two_pass=pipeline in TWO_PASS)
+        assert st["depth_bits_differ"] == 0, (trial, st)
+        if pipeline != "specular":
+            assert st["rgb_exact_frac"] == 1.0, (trial, st)
+        if pipeline in TWO_PASS:
+            assert np.array_equal(g.raw_shadow().view(np.uint32), o.raw_shadow().view(np.uint32)), trial
+        # The oracle, like the reference, runs the fragment closure for every fragment that passes the z-test when it
+        # is drawn, the backend only for the final winner of a pixel: its event counts cover the visible fragments,
+        # a subset of the oracle's.
+        dg, do = g.diagnostics(), o.diagnostics()
+        for k in ("shadow_index_oob", "shadow_x_wrap", "texel_oob", "nan_depth"):
+            assert dg[k] <= do[k], (trial, k, dg, do)
+        done += 1
+        g.close()
+    assert done >= 5

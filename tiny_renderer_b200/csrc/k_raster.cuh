@@ -170,13 +170,15 @@ __device__ __noinline__ BlockState load_block_state(const unsigned long long* ke
 }
 
 template <int MODE>
-__global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u, const __grid_constant__ CUtensorMap rgb_map) {
+__global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u, const __grid_constant__ CUtensorMap rgb_map,
+                                         const __grid_constant__ CUtensorMap rgb_map_top) {
     constexpr bool DEPTH_ONLY = MODE == kModeDepthOnly;
     constexpr bool SHADE = MODE >= 0;
     constexpr int kRgbRow = kTileW * 3;
     __shared__ __align__(16) float s_tri[kListCap * kStageWords];
     __shared__ uint32_t s_mask[kListCap], s_maskx[kListCap];   // per staged polygon: blocks to visit (exact / literal path)
-    // the tile's RGB in frame order (top-down: tile row r at s_rgb row kTileH-1-r), the box of the TMA store
+    // the tile's RGB in frame order (top-down: tile row r at s_rgb row rows-1-r, rows = the tile's on-screen rows), the
+    // box of the TMA store
     __shared__ __align__(128) uint8_t s_rgb[SHADE ? kTileH * kRgbRow : 16];
     __shared__ int s_warp_count[kRasterThreads / 32];
     __shared__ int s_count;
@@ -349,7 +351,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
             if (SHADE && !more) {
                 // ---- (3) fragment stage for the winners that passed the depth test in THIS render; one copy of the
                 //      fragment code (the pixel's state is selected into scalars) keeps the kernel in the instruction cache
-                uint8_t* const tile_px = s_rgb + (kTileH - 1 - ly) * kRgbRow + lx * 3;
+                uint8_t* const tile_px = s_rgb + (ty1 - ty0 - ly) * kRgbRow + lx * 3;
 #pragma unroll 1
                 for (int k = 0; k < kPix; ++k) {
                     const bool second = k != 0;
@@ -371,8 +373,10 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
                         out = shade_pixel<SHADE ? MODE : 0>(sa, u, lo & kTriMask, px, qy, z, v0, v1, v2);
                     }
                     if (rgb_bulk) {
-                        uint8_t* p = tile_px - k * (4 * kRgbRow);
-                        p[0] = (uint8_t)out; p[1] = (uint8_t)(out >> 8); p[2] = (uint8_t)(out >> 16);
+                        if (qy <= ty1) {                // (rows of a partial top tile beyond the frame have no place in s_rgb)
+                            uint8_t* p = tile_px - k * (4 * kRgbRow);
+                            p[0] = (uint8_t)out; p[1] = (uint8_t)(out >> 8); p[2] = (uint8_t)(out >> 16);
+                        }
                     } else if (shaded) {
                         uint8_t* p = sa.rgb + ((size_t)(a.height - 1 - qy) * a.width + px) * 3;
                         p[0] = (uint8_t)out; p[1] = (uint8_t)(out >> 8); p[2] = (uint8_t)(out >> 16);
@@ -423,20 +427,24 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncthreads();
         }
+        const int rows = ty1 - ty0 + 1;
         if (sa.rgb_tma) {
             if (tid == 0) {
+                // Box coordinates must not be negative (the store faults), so the partial tile row at the top of the
+                // frame has its own tensor map whose box is as high as that row; clipping on the high side (the right
+                // border) is done by the hardware.
                 const uint32_t src = (uint32_t)__cvta_generic_to_shared(s_rgb);
-                const int x = tx0 * 3, y = (int)a.height - ty0 - kTileH;        // y < 0 on a partial top tile row: clipped
+                const int x = tx0 * 3, y = (int)a.height - ty0 - rows;
+                const uint64_t map = reinterpret_cast<uint64_t>(rows == kTileH ? &rgb_map : &rgb_map_top);
                 asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-                             :: "l"(reinterpret_cast<uint64_t>(&rgb_map)), "r"(src), "r"(x), "r"(y) : "memory");
+                             :: "l"(map), "r"(src), "r"(x), "r"(y) : "memory");
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             }
         } else {
-            const int rows = ty1 - ty0 + 1;
             for (int i = tid; i < rows * row_bytes; i += kRasterThreads) {
                 int r = i / row_bytes, c = i % row_bytes;
-                sa.rgb[((size_t)(a.height - 1 - (ty0 + r)) * a.width + tx0) * 3 + c] = s_rgb[(kTileH - 1 - r) * kRgbRow + c];
+                sa.rgb[((size_t)(a.height - 1 - (ty0 + r)) * a.width + tx0) * 3 + c] = s_rgb[(rows - 1 - r) * kRgbRow + c];
             }
         }
         if (tid == 0) sa.rgb_zero[tile] = touched ? 0u : 1u;

@@ -53,6 +53,7 @@ struct tr_scene {
         uint32_t* rgb_zero = nullptr;
         uint32_t* shadow_clear = nullptr;
         CUtensorMap rgb_map{};             // rgb as a (width*3 bytes) x height u8 tensor, box = one raster tile
+        CUtensorMap rgb_map_top{};         // same tensor, box as high as the partial tile row at the top of the frame
         bool rgb_tma = false;
         SetupOut cam{}, lit{};
         Bins bins{};
@@ -148,12 +149,17 @@ int make_rgb_map(tr_scene* s, tr_scene::Slot* sl) {
         return fail(TR_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
     const cuuint64_t dims[2] = {(cuuint64_t)s->width * 3, (cuuint64_t)s->height};
     const cuuint64_t pitch[1] = {(cuuint64_t)s->width * 3};
-    const cuuint32_t box[2] = {(cuuint32_t)kTileW * 3, (cuuint32_t)kTileH};
     const cuuint32_t step[2] = {1, 1};
-    CUresult r = reinterpret_cast<EncodeTiled>(fn)(&sl->rgb_map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, sl->rgb, dims, pitch, box, step,
-                                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                                   CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail(TR_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for a %ux%u frame", (int)r, s->width, s->height);
+    const uint32_t top_rows = s->height % kTileH ? s->height % kTileH : kTileH;
+    CUtensorMap* maps[2] = {&sl->rgb_map, &sl->rgb_map_top};
+    const uint32_t box_rows[2] = {std::min<uint32_t>(kTileH, s->height), top_rows};
+    for (int k = 0; k < 2; ++k) {
+        const cuuint32_t box[2] = {(cuuint32_t)kTileW * 3, (cuuint32_t)box_rows[k]};
+        CUresult r = reinterpret_cast<EncodeTiled>(fn)(maps[k], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, sl->rgb, dims, pitch, box, step,
+                                                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                       CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(TR_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for a %ux%u frame", (int)r, s->width, s->height);
+    }
     sl->rgb_tma = true;
     return TR_OK;
 }
@@ -397,7 +403,7 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     a.tile_order = s->tile_order + (s->overlapping ? (size_t)s->tiles_x * s->tiles_y : 0);
     dim3 grid(s->tiles_x * s->tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
-#define TR_RASTER(M) k_raster<M><<<grid, kRasterThreads, 0, s->stream>>>(a, sa, u, S(s).rgb_map)
+#define TR_RASTER(M) k_raster<M><<<grid, kRasterThreads, 0, s->stream>>>(a, sa, u, S(s).rgb_map, S(s).rgb_map_top)
     switch (mode) {
         case kModeDepthOnly: TR_RASTER(kModeDepthOnly); break;
         case kModeVisibility: TR_RASTER(kModeVisibility); break;
