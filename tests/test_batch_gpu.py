@@ -220,3 +220,71 @@ def test_occlusion_division_forms_agree(tinyr):
     assert sums[0].sum() > 0
     assert np.array_equal(sums[0], sums[1])
     assert np.array_equal(frames[0], frames[1])
+
+
+def _fuzz_views(rng, n, close=False):
+    views = np.zeros((n, 12), np.float32)
+    for k in range(n):
+        d = rng.normal(size=3)
+        d /= np.linalg.norm(d)
+        views[k, 0:3] = d * (rng.uniform(0.15, 0.45) if close else rng.uniform(0.45, 2.5))
+        views[k, 3:6] = rng.uniform(-0.6, 0.6, 3) * (k % 3 != 0)
+        views[k, 6:9] = (rng.uniform(-0.3, 0.3), 1.0, rng.uniform(-0.3, 0.3))
+        l = rng.normal(size=3)
+        views[k, 9:12] = l / np.linalg.norm(l)
+    return views
+
+
+@pytest.mark.parametrize("pipeline,ring", [("phong", 1), ("phong", 3), ("shadow", 2), ("darboux", 4)])
+def test_view_batch_with_unrelated_views_keeps_tile_state_right(tinyr, pipeline, ring):
+    """Frame slots are reused by views that have nothing in common (the model jumps around, fills the frame, leaves
+    it): the per-tile flags — keys stale, RGB already zero, shadow depths already cleared — must never let a stale
+    tile through.  Every frame of the batch equals the same view rendered by a scene created for it; frame sizes
+    with partial tiles on the top and right."""
+    from tiny_renderer_b200.scene import Scene
+    m = get_model("diablo")
+    w, h = 400, 250
+    rng = np.random.default_rng(77 + ring)
+    views = _fuzz_views(rng, 14)
+    views[5, 0:3] *= 40.0                                   # a view whose model is a speck: nearly every tile turns empty again
+    g = Scene(w, h, m, pipeline, ring=ring)
+    frames = np.zeros((len(views), h, w, 3), np.uint8)
+    g.render_views(views, want_checksums=False, frames_out=frames)
+    for k in range(len(views)):
+        single = Scene(w, h, m, pipeline)
+        parity.drive(single, views[k, 0:3], views[k, 3:6], views[k, 6:9], views[k, 9:12])
+        assert np.array_equal(single.get_frame_buffer(), frames[k]), k
+        if k == len(views) - 1:                             # the scene is left on the last view, with its buffers
+            assert np.array_equal(single.raw_z(), g.raw_z())
+            assert np.array_equal(single.raw_visibility(), g.raw_visibility())
+            if pipeline == "shadow":
+                assert np.array_equal(single.raw_shadow().view(np.uint32), g.raw_shadow().view(np.uint32))
+        single.close()
+    g.close()
+
+
+@pytest.mark.parametrize("pipeline", ["phong", "shadow", "occlusion"])
+def test_fuzz_cameras_inside_the_model(tinyr, oracle, pipeline):
+    """Cameras 0.15-0.45 from the origin: polygons many times larger than the frame (the literal raster path, long
+    per-tile lists), most of the model off screen."""
+    from tiny_renderer_b200.scene import Scene
+    rng = np.random.default_rng(991)
+    w, h = 272, 200
+    views = _fuzz_views(rng, 6, close=True)
+    done = 0
+    for k, v in enumerate(views):
+        model = get_model("african_head" if k % 2 else "diablo")
+        g = Scene(w, h, model, pipeline)
+        o = oracle.OracleScene(w, h, model, pipeline)
+        o.clear(); o.set_light_direction(v[9:12]); o.set_camera(v[0:3], v[3:6], v[6:9])
+        if o.render(allow_panic=True):
+            with pytest.raises(tinyr.TinyrError):
+                parity.drive(g, v[0:3], v[3:6], v[6:9], v[9:12])
+            g.close()
+            continue
+        parity.drive(g, v[0:3], v[3:6], v[6:9], v[9:12])
+        st = parity.compare(g, o, two_pass=pipeline != "phong")
+        assert st["depth_bits_differ"] == 0 and st["rgb_exact_frac"] == 1.0, (k, st)
+        done += 1
+        g.close()
+    assert done >= 3
