@@ -288,3 +288,32 @@ def test_fuzz_cameras_inside_the_model(tinyr, oracle, pipeline):
         done += 1
         g.close()
     assert done >= 3
+
+
+def test_ao_batch_with_unfiltered_lights(tinyr, oracle):
+    """Many-light AO with directions that are NOT filtered by the generator: the model leaves the light's frame, shadow
+    lookups fall outside the buffer (the reference would panic there; both sides count the event and read the cleared
+    value) and the camera is off-centre.  Sums must still be identical."""
+    from tiny_renderer_b200.scene import Scene
+    m = get_model("diablo")
+    w, h = 240, 176
+    rng = np.random.default_rng(4242)
+    cam = _fuzz_views(rng, 3)
+    for c in cam:
+        lights = []
+        o = oracle.OracleScene(w, h, m, "occlusion")
+        o.set_camera(c[0:3], c[3:6], c[6:9])
+        while len(lights) < 6:
+            l = rng.normal(size=3).astype(np.float32)
+            l /= np.linalg.norm(l)
+            o.clear(); o.set_light_direction(l)
+            if o.render(allow_panic=True) == 0:             # the reference can prepare this light
+                lights.append(l)
+        lights = np.array(lights, np.float32)
+        g = Scene(w, h, m, "occlusion", ring=2)
+        g.set_camera(c[0:3], c[3:6], c[6:9])
+        total = g.render_ao(lights)
+        o2 = oracle.OracleScene(w, h, m, "occlusion")
+        o2.set_camera(c[0:3], c[3:6], c[6:9])
+        assert np.array_equal(total, o2.render_ao(lights))
+        g.close()
