@@ -266,3 +266,24 @@ def test_fuzz_cameras_partly_off_screen(tinyr, oracle, pipeline):
         done += 1
         g.close()
     assert done >= 5
+
+
+@pytest.mark.parametrize("pipeline", ["phong", "darboux"])
+def test_4k_view_reaches_top_and_right_border(tinyr, oracle, pipeline):
+    """3840x2160 has a half-height tile row at the top (2160 = 67.5 x 32): a view whose model runs off the top and the
+    right border draws into it (the TMA store of that row has its own tensor map) and into the last tile column."""
+    model = get_model("diablo")
+    from tiny_renderer_b200.scene import Scene
+    g = Scene(3840, 2160, model, pipeline)
+    o = oracle.OracleScene(3840, 2160, model, pipeline)
+    lf = np.array([-0.6138697862625122, -0.4760490953922272, -0.6958363652229309], np.float32)
+    la = np.array([0.6074419021606445, -0.6972569227218628, 0.28669044375419617], np.float32)
+    up = np.array([0.22205309569835663, 1.0, -0.1636088788509369], np.float32)
+    light = np.array([0.4, 0.3, 0.85], np.float32)
+    parity.drive(g, lf, la, up, light)
+    parity.drive(o, lf, la, up, light)
+    st = parity.compare(g, o, rgb_frac=1.0)
+    vis = g.raw_visibility()                                # bottom-up rows
+    assert (vis[-1] != 0xFFFFFFFF).any() and (vis[:, -1] != 0xFFFFFFFF).any()     # top row and last column are drawn into
+    assert st["depth_bits_differ"] == 0
+    g.close()
