@@ -287,3 +287,40 @@ def test_4k_view_reaches_top_and_right_border(tinyr, oracle, pipeline):
     assert (vis[-1] != 0xFFFFFFFF).any() and (vis[:, -1] != 0xFFFFFFFF).any()     # top row and last column are drawn into
     assert st["depth_bits_differ"] == 0
     g.close()
+
+
+@pytest.mark.parametrize("pipeline", ["phong", "darboux", "shadow", "occlusion"])
+def test_fuzz_sequences_with_and_without_clear(tinyr, oracle, pipeline):
+    """One scene driven through a random sequence of views where only some renders are preceded by `clear`
+    (scene.rs contract: render does not clear): frames pile up on the old depth buffer, tiles move between the cleared,
+    stale and drawn states, and after every render all buffers must equal the oracle's."""
+    from tiny_renderer_b200.scene import Scene
+    rng = np.random.default_rng(31337 + PIPELINES.index(pipeline))
+    model = get_model("diablo")
+    w, h = 336, 250
+    g = Scene(w, h, model, pipeline)
+    o = oracle.OracleScene(w, h, model, pipeline)
+    rendered = 0
+    for step in range(9):
+        d = rng.normal(size=3)
+        d /= np.linalg.norm(d)
+        lf = (d * rng.uniform(0.5, 2.5)).astype(np.float32)
+        la = (rng.uniform(-0.5, 0.5, 3) * (step % 2)).astype(np.float32)
+        up = np.array([rng.uniform(-0.2, 0.2), 1.0, rng.uniform(-0.2, 0.2)], np.float32)
+        l = rng.normal(size=3)
+        light = (l / np.linalg.norm(l)).astype(np.float32)
+        clear = step == 0 or rng.random() < 0.5
+        if clear:
+            o.clear()
+        o.set_light_direction(light); o.set_camera(lf, la, up)
+        if o.render(allow_panic=True):
+            break               # the reference would have panicked here: nothing left to compare on this scene
+        parity.drive(g, lf, la, up, light, clear=clear)
+        st = parity.compare(g, o, two_pass=pipeline in TWO_PASS)
+        assert st["depth_bits_differ"] == 0 and st["rgb_exact_frac"] == 1.0, (step, clear, st)
+        rendered += 1
+    assert rendered >= 4
+    g.clear(); o.clear()
+    assert np.array_equal(g.get_frame_buffer(), o.get_frame_buffer())
+    assert np.array_equal(g.raw_z(), o.raw_z())
+    g.close()
