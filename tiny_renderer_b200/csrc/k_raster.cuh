@@ -180,7 +180,6 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     // the tile's RGB in frame order (top-down: tile row r at s_rgb row rows-1-r, rows = the tile's on-screen rows), the
     // box of the TMA store
     __shared__ __align__(128) uint8_t s_rgb[SHADE ? kTileH * kRgbRow : 16];
-    __shared__ int s_warp_count[kRasterThreads / 32];
     __shared__ int s_count;
     __shared__ int s_next;
     __shared__ int s_block;                                 // next block of the tile to hand to a warp
@@ -214,8 +213,15 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         // ---- (1) filter the source list (cell bin, or all polygons) against the tile, kListCap polygons per round ----
         if (tid == 0) { s_count = 0; s_next = (int)n_src; s_block = 0; s_inexact = 0; }
         __syncthreads();
-        for (uint32_t base = scan_from; base < n_src; base += kRasterThreads) {
-            uint32_t i = base + tid, t = 0;
+        // Warps walk the list independently (no barrier per step): a warp ballots its 32 entries, reserves slots for
+        // the hits with one shared atomic and stages them.  The order of the staged list therefore varies from run to
+        // run; the result does not (winners are ordered by depth and polygon id, never by list position).  When the
+        // list overflows, s_next ends up at the smallest source index that was not staged and the next round restarts
+        // there; entries beyond it that did get a slot are staged again, which changes nothing (an equal key never
+        // beats itself).
+        for (uint32_t base = scan_from + warp * 32; base < n_src; base += kRasterThreads) {
+            if (*(volatile int*)&s_count >= kListCap) { if (lane == 0) atomicMin(&s_next, (int)base); break; }
+            uint32_t i = base + lane, t = 0;
             bool hit = false;
             int4 bb = make_int4(1, 0, 0, 0);
             if (i < n_src) {
@@ -223,21 +229,17 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
                 bb = __ldg(&a.bbox[t]);
                 hit = bb.x <= bb.z && bb.x <= tx1 && bb.z >= tx0 && bb.y <= ty1 && bb.w >= ty0;
             }
-            unsigned m = __ballot_sync(0xffffffffu, hit);
-            if (lane == 0) s_warp_count[warp] = __popc(m);
-            __syncthreads();
-            int before = s_count, total = 0;
-            for (int w = 0; w < kRasterThreads / 32; ++w) { int c = s_warp_count[w]; if (w < warp) before += c; total += c; }
-            int slot = before + __popc(m & ((1u << lane) - 1u));
-            bool overflow = s_count + total > kListCap;
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (m == 0u) continue;
+            int first = 0;
+            if (lane == 0) first = atomicAdd(&s_count, __popc(m));
+            first = __shfl_sync(0xffffffffu, first, 0);
+            const int slot = first + __popc(m & ((1u << lane) - 1u));
             if (hit && slot < kListCap) stage_polygon(a, t, bb, slot, tx0, ty0, tx1, ty1, s_tri, s_mask, s_maskx, &s_inexact);
-            if (hit && slot >= kListCap) atomicMin(&s_next, (int)i);       // first source entry that did not fit
-            __syncthreads();
-            if (tid == 0) s_count = min(s_count + total, kListCap);
-            __syncthreads();
-            if (overflow) break;
+            if (hit && slot >= kListCap) atomicMin(&s_next, (int)i);       // a source entry that did not fit
         }
-        const int n_list = s_count;
+        __syncthreads();
+        const int n_list = min(s_count, kListCap);
         const int n_inexact = s_inexact;
         scan_from = (uint32_t)s_next;       // == n_src when everything was staged
         more = scan_from < n_src;
