@@ -227,8 +227,8 @@ AO_LIGHTS = 1024
 
 def run_ao(args, rank, world, dev, model, dist, stream):
     """BASELINE config 4: diablo, occlusion pipeline, 1024 light-direction depth passes at 3840x2160, lights sharded
-    over the ranks (strong scaling: the light count is fixed), ONE all-reduce(sum) of the u32 accumulators at the
-    end.  Device-timed (CUDA events on the launching stream), max over ranks."""
+    over the ranks (strong scaling: the light count is fixed), ONE sum of the u32 accumulators over the ranks at the
+    end (the library's kernel over NVLink peer memory).  Device-timed (CUDA events on the launching stream), max over ranks."""
     import torch
     import tiny_renderer_b200 as tr
     from tiny_renderer_b200 import multi
@@ -239,10 +239,28 @@ def run_ao(args, rank, world, dev, model, dist, stream):
     lf, la, up, _ = __import__("assets").view_vectors(0.0, 0.0)
     s.set_camera(lf, la, up)
     lo, hi = multi.shard_range(len(lights), rank, world)
+    # The sum over the ranks is the library's own kernel over NVLink peer memory (k_peer.cuh), on the scene stream
+    # behind the light passes; the NCCL all-reduce of the same buffer is timed beside it on a copy, for comparison.
+    multi.connect_ao_peers(s, rank, world)
     s.render_ao(lights[lo:min(hi, lo + 8)], reset=True, read=False)          # warm-up
     acc = multi.ao_accumulator_tensor(s)
+    nccl_ms = None
     if dist is not None:
-        dist.all_reduce(acc)
+        s.ao_reduce_peers()
+        s.synchronize()
+        scratch = acc.clone()
+        for _ in range(3):
+            dist.all_reduce(scratch)
+        torch.cuda.synchronize()
+        dist.barrier()
+        n0, n1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0.record()
+        for _ in range(5):
+            dist.all_reduce(scratch)
+        n1.record()
+        torch.cuda.synchronize()
+        nccl_ms = n0.elapsed_time(n1) / 5
+        del scratch
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
@@ -250,25 +268,28 @@ def run_ao(args, rank, world, dev, model, dist, stream):
     e0.record()
     s.render_ao(lights[lo:hi], reset=True, read=False)
     e1.record()
-    multi.allreduce_ao(acc)
+    if world > 1:
+        s.ao_reduce_peers()
     e2.record()
     torch.cuda.synchronize()
     ms, ar_ms = e0.elapsed_time(e2), e1.elapsed_time(e2)
     if dist is not None:
-        t = torch.tensor([ms, ar_ms], device="cuda", dtype=torch.float64)
+        t = torch.tensor([ms, ar_ms, nccl_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, ar_ms = float(t[0].item()), float(t[1].item())
+        ms, ar_ms, nccl_ms = float(t[0].item()), float(t[1].item()), float(t[2].item())
     total = s.read_ao()
     covered = int((s.raw_visibility() != 0xFFFFFFFF).sum())
     diag = s.diagnostics()
+    del acc
+    multi.disconnect_ao_peers(s, world)
     s.close()
     n_px = W4K * H4K
     per_pass_bytes = 8 * n_px + 8 * covered              # shadow write + one read + u32 accumulate RMW
     peak, _ = load_peaks()
     us_per_pass = ms * 1e3 / max(1, hi - lo)
     return {"metric": "AO depth passes/s", "value": AO_LIGHTS / (ms * 1e-3), "unit": "passes/s", "n_gpus": world,
-            "scaling": "strong", "lights": AO_LIGHTS, "lights_per_gpu": hi - lo, "ms": ms, "allreduce_ms": ar_ms,
-            "allreduce_bytes": 4 * n_px, "us_per_pass": us_per_pass, "checksum": int(total.astype(np.uint64).sum()),
+            "scaling": "strong", "lights": AO_LIGHTS, "lights_per_gpu": hi - lo, "ms": ms, "exchange": "k_ao_reduce_peers (own kernel, NVLink peer memory)" if world > 1 else "none",
+            "exchange_ms": ar_ms, "nccl_allreduce_ms": nccl_ms, "exchange_bytes": 4 * n_px, "us_per_pass": us_per_pass, "checksum": int(total.astype(np.uint64).sum()),
             "shadow_index_oob": diag["shadow_index_oob"], "shadow_x_wrap": diag["shadow_x_wrap"],
             "roofline": {"bound": "hbm", "algorithmic_bytes_per_pass": per_pass_bytes,
                          "achieved": per_pass_bytes / (us_per_pass * 1e-6) / 1e9, "peak": peak,

@@ -112,6 +112,21 @@ int tr_scene_render_views(tr_scene* s, const tr_view* views, uint32_t n_views, u
 int tr_scene_render_ao(tr_scene* s, const float* light_dirs_xyz, uint32_t n_lights, int reset, uint32_t* accum_host);
 int tr_scene_ao_device_buffer(tr_scene* s, void** device_ptr_u32, size_t* n_elements);
 int tr_scene_read_ao(tr_scene* s, uint32_t* accum_host);
+/* Multi-GPU sum of the accumulators, one process per GPU (the reference renders its
+ * light passes in one loop on one device, shader.rs:806-963, so there is no reference interface to cite: this is the
+ * exchange step of the sharded batch).  Lights are split over the ranks, every rank runs tr_scene_render_ao on its
+ * share, then ONE kernel per rank adds the accumulators over NVLink peer memory (k_peer.cuh): no NCCL call, no host
+ * staging; afterwards every rank's accumulator holds the total (u32 sums: bit-identical for any rank count).
+ *   tr_scene_ao_ipc_handle    64-byte CUDA IPC handle of this scene's accumulator, to be passed to the other ranks
+ *   tr_scene_ao_open_peers    handles = world x 64 bytes in rank order (entry `rank` is ignored); world <= 16; world == 1
+ *                             needs no handles.  Maps the peers' accumulators; call again after the set of ranks changes
+ *   tr_scene_ao_reduce_peers  collective, asynchronous on the scene stream: every rank calls it once per reduction.  A
+ *                             rank that never arrives makes the others time out after 10 s: tr_scene_read_ao then fails
+ *   tr_scene_ao_close_peers   unmaps (also done by tr_scene_destroy) */
+int tr_scene_ao_ipc_handle(tr_scene* s, void* handle64);
+int tr_scene_ao_open_peers(tr_scene* s, const void* handles, uint32_t world, uint32_t rank);
+int tr_scene_ao_reduce_peers(tr_scene* s);
+int tr_scene_ao_close_peers(tr_scene* s);
 uint64_t tr_checksum_rgb8(const uint8_t* rgb8, size_t n_bytes);                  /* host twin of the device checksum */
 /* Deterministic light set for tr_scene_render_ao (host only): SplitMix64(seed) -> uniform sphere directions, computed
  * in double and rounded to f32, rejecting directions on which the reference's occlusion pipeline panics or reads

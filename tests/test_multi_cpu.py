@@ -99,6 +99,14 @@ def _ao_worker(rank, world, port, lights, out_dir):
     mine = np.arange(lo, hi, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15)
     allc = multi.gather_checksums(mine, 10, rank, world)
     np.save(os.path.join(out_dir, "cs_%d.npy" % rank), allc)
+    # peer exchange, host side: every rank ends up with all handles in rank order and the reduce hook gets the
+    # object render_slice returned (the device kernel itself is covered by tests/test_multi_gpu.py)
+    handles = multi.exchange_handles(bytes([rank + 1]) * 64)
+    assert handles == [bytes([r + 1]) * 64 for r in range(world)]
+    seen = []
+    multi.ao_sharded(lambda ls: ("acc", len(ls)), lights, rank, world, reduce=lambda acc, g: seen.append((acc, g)))
+    lo, hi = multi.shard_range(len(lights), rank, world)
+    assert seen == [(("acc", hi - lo), None)]
     dist.destroy_process_group()
 
 

@@ -94,6 +94,8 @@ def lib():
             "tr_scene_diagnostics": [vp, vp], "tr_scene_get_uniforms": [vp, vp],
             "tr_scene_render_views": [vp, vp, u32, vp, vp], "tr_scene_render_ao": [vp, vp, u32, i32, vp],
             "tr_scene_ao_device_buffer": [vp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)], "tr_scene_read_ao": [vp, vp],
+            "tr_scene_ao_ipc_handle": [vp, vp], "tr_scene_ao_open_peers": [vp, vp, u32, u32],
+            "tr_scene_ao_reduce_peers": [vp], "tr_scene_ao_close_peers": [vp],
             "tr_device_count": [ctypes.POINTER(i32)], "tr_scene_set_stream": [vp, vp],
             "tr_scene_device_frame": [vp, ctypes.POINTER(vp)], "tr_scene_timer_begin": [vp],
             "tr_scene_timer_end": [vp, ctypes.POINTER(ctypes.c_float)], "tr_scene_set_profiling": [vp, i32],

@@ -9,6 +9,7 @@
 #include "k_raster.cuh"
 #include "k_shade.cuh"
 #include "k_misc.cuh"
+#include "k_peer.cuh"
 
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -25,6 +26,10 @@ using namespace tr;
         cudaError_t e_ = (call);                                                                         \
         if (e_ != cudaSuccess) return fail(TR_ERR_CUDA, "%s -> %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
+
+// u32 words of the AO allocation: the sums, zero padding to whole uint4, the barrier flags of K9 (k_peer.cuh)
+static inline size_t ao_vec_count(size_t n_px) { return (n_px + 3) / 4; }
+static inline size_t ao_alloc_words(size_t n_px) { return ao_vec_count(n_px) * 4 + kPeerFlagWords; }
 
 enum KernelSlot { KS_SETUP = 0, KS_BIN, KS_RASTER, KS_SHADOW, KS_SHADE, KS_AO, KS_CLEAR, KS_CHECKSUM, KS_COUNT };
 
@@ -67,7 +72,11 @@ struct tr_scene {
     uint32_t* tile_order = nullptr;
     bool overlapping = false;            // a batch is running frames / light passes concurrently on the slot streams
     uint32_t debug_flags = 0;            // tr_scene_set_debug_flags -> Uniforms::debug_flags
-    uint32_t* ao = nullptr;
+    uint32_t* ao = nullptr;            // n_px sums, zero padding to a multiple of 4, then the kPeerFlagWords barrier flags of K9
+    // K9 (k_peer.cuh): the accumulators of all ranks, mapped through CUDA IPC by tr_scene_ao_open_peers
+    uint32_t* peer_buf[kMaxPeers] = {};
+    uint32_t peer_world = 0, peer_rank = 0, peer_value = 1;
+    int* peer_status = nullptr;        // mapped host word the kernel sets when a barrier times out
     AoList ao_list{};                  // covered pixels of the camera view (many-light AO batch), allocated on first use
     uint32_t ao_list_n = 0;
     unsigned long long* diag = nullptr;
@@ -325,8 +334,8 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
         CU(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
     }
-    CU(cudaMalloc(&s->ao, s->n_px * 4));
-    CU(cudaMemset(s->ao, 0, s->n_px * 4));
+    CU(cudaMalloc(&s->ao, ao_alloc_words(s->n_px) * 4));
+    CU(cudaMemset(s->ao, 0, ao_alloc_words(s->n_px) * 4));
     CU(cudaMalloc(&s->diag, D_COUNT * 8));
     CU(cudaMemset(s->diag, 0, D_COUNT * 8));
     const tr_image* imgs[4] = {&d->texture, &d->normal_map, &d->normal_map_tangent, &d->specular_map};
@@ -339,10 +348,19 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
     return TR_OK;
 }
 
+void close_peers(tr_scene* s) {
+    for (uint32_t r = 0; r < s->peer_world; ++r)
+        if (r != s->peer_rank && s->peer_buf[r]) cudaIpcCloseMemHandle(s->peer_buf[r]);
+    for (auto& p : s->peer_buf) p = nullptr;
+    s->peer_world = 0;
+}
+
 void destroy_impl(tr_scene* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
+    close_peers(s);
+    if (s->peer_status) cudaFreeHost(s->peer_status);
     for (auto& sp : s->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : s->event_pool) cudaEventDestroy(e);
     if (s->ev_begin) cudaEventDestroy(s->ev_begin);

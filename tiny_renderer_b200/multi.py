@@ -4,9 +4,11 @@
 * view batches (BASELINE config 5): independent units, contiguous blocks of views per rank, NO data-path
   collective; only the 8-byte per-view checksums are gathered (control plane).
 * many-light ambient occlusion (BASELINE config 4): lights sharded, every rank accumulates its slice into its own
-  u32 buffer (camera visibility is recomputed per rank: cheaper than broadcasting 66 MB of keys), then ONE
-  all-reduce(sum) of W*H u32 values.  Integer sums make the result independent of the rank count and of the
-  collective's algorithm, hence bit-identical for 1/2/4/8 GPUs.
+  u32 buffer (camera visibility is recomputed per rank: cheaper than broadcasting 66 MB of keys), then ONE sum of
+  the W*H u32 values over the ranks.  Integer sums make the result independent of the rank count and of the
+  exchange's algorithm, hence bit-identical for 1/2/4/8 GPUs.  Two exchanges: the library's own kernel over NVLink
+  peer memory (connect_ao_peers + Scene.ao_reduce_peers: no host synchronisation, stays on the scene stream; the
+  default on GPUs) and a torch.distributed all-reduce (allreduce_ao: NCCL on GPUs, gloo in the CPU tests).
 
 Single frames (configs 1-3) do not shard: replicas only.
 """
@@ -43,27 +45,68 @@ def allreduce_ao(accum, group=None):
     return accum
 
 
-def ao_sharded(render_slice, light_dirs, rank, world, group=None):
-    """Backend-independent core of config 4: `render_slice(lights[lo:hi])` must return this rank's accumulator as
-    an int32 torch tensor on the process group's device; the summed tensor is returned (in place)."""
+def ao_sharded(render_slice, light_dirs, rank, world, group=None, reduce=allreduce_ao):
+    """Backend-independent core of config 4: `render_slice(lights[lo:hi])` returns this rank's accumulator and
+    `reduce(accumulator, group)` sums it over the ranks (default: an int32 torch tensor on the process group's
+    device, all-reduced in place)."""
     lights = np.ascontiguousarray(light_dirs, np.float32).reshape(-1, 3)
     lo, hi = shard_range(len(lights), rank, world)
-    return allreduce_ao(render_slice(lights[lo:hi]), group)
+    return reduce(render_slice(lights[lo:hi]), group)
 
 
-def render_ao_sharded(scene, light_dirs, rank, world, group=None, read=True):
+def exchange_handles(mine, group=None):
+    """Every rank's 64-byte IPC handle, in rank order (control plane: one all_gather_object)."""
+    import torch.distributed as dist
+    handles = [None] * dist.get_world_size(group)
+    dist.all_gather_object(handles, bytes(mine), group=group)
+    if any(h is None or len(h) != len(mine) for h in handles):
+        raise RuntimeError("a rank sent no handle")
+    return handles
+
+
+def connect_ao_peers(scene, rank, world, group=None):
+    """Maps the other ranks' AO accumulators into `scene` (once per scene; collective).  Afterwards
+    scene.ao_reduce_peers() sums the accumulators with the library's own kernel over NVLink."""
+    if world == 1:
+        scene.ao_open_peers([b"\0" * 64], 0)
+        return
+    import torch.distributed as dist
+    scene.ao_open_peers(exchange_handles(scene.ao_ipc_handle(), group), rank)
+    dist.barrier(group)                 # nobody starts a reduction before every rank has mapped every accumulator
+
+
+def disconnect_ao_peers(scene, world, group=None):
+    """Unmaps the peers' accumulators; collective, and to be called before any rank closes its scene (an exporter
+    must not free memory that other processes still have mapped)."""
+    scene.ao_close_peers()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier(group)
+
+
+def render_ao_sharded(scene, light_dirs, rank, world, group=None, read=True, exchange="peer"):
     """Config 4: this rank renders lights [lo, hi) into the scene's accumulator, then the accumulators are summed
     over the ranks.  Returns the (H, W) u32 total on every rank (or None when read=False; the total then stays in
-    the scene's device accumulator)."""
-    import torch
+    the scene's device accumulator).  exchange="peer": the library's kernel over NVLink peer memory (needs
+    connect_ao_peers first); "allreduce": torch.distributed."""
+    if exchange == "peer":
+        def render_slice(lights):
+            scene.render_ao(lights, reset=True, read=False)
+            return scene
 
-    def render_slice(lights):
-        scene.render_ao(lights, reset=True, read=False)
-        scene.synchronize()             # the scene renders on its own stream; the collective runs on torch's
-        return ao_accumulator_tensor(scene)
+        ao_sharded(render_slice, light_dirs, rank, world, group, reduce=lambda s, _g: s.ao_reduce_peers() if world > 1 else None)
+    elif exchange == "allreduce":
+        import torch
 
-    ao_sharded(render_slice, light_dirs, rank, world, group)
-    torch.cuda.current_stream().synchronize()
+        def render_slice(lights):
+            scene.render_ao(lights, reset=True, read=False)
+            scene.synchronize()         # the scene renders on its own stream; the collective runs on torch's
+            return ao_accumulator_tensor(scene)
+
+        ao_sharded(render_slice, light_dirs, rank, world, group)
+        torch.cuda.current_stream().synchronize()
+    else:
+        raise ValueError("exchange is 'peer' or 'allreduce'")
     return scene.read_ao() if read else None
 
 

@@ -242,6 +242,28 @@ class Scene:
     def read_ao(self):
         return self._read("tr_scene_read_ao", (self.height, self.width), np.uint32)
 
+    # Multi-GPU sum of the AO accumulators over NVLink peer memory (include/tinyr.h; one process per GPU).
+    def ao_ipc_handle(self):
+        """64-byte CUDA IPC handle of this scene's accumulator, for the other ranks' ao_open_peers."""
+        h = ctypes.create_string_buffer(64)
+        _check(lib().tr_scene_ao_ipc_handle(self._h, h))
+        return h.raw
+
+    def ao_open_peers(self, handles, rank):
+        """handles: one 64-byte handle per rank, in rank order (this rank's own entry is ignored)."""
+        world = len(handles)
+        if any(len(h) != 64 for h in handles):
+            raise ValueError("every handle is 64 bytes")
+        blob = ctypes.create_string_buffer(b"".join(handles), 64 * world)
+        _check(lib().tr_scene_ao_open_peers(self._h, blob, world, rank))
+
+    def ao_reduce_peers(self):
+        """Collective over the ranks of ao_open_peers; asynchronous on the scene stream."""
+        _check(lib().tr_scene_ao_reduce_peers(self._h))
+
+    def ao_close_peers(self):
+        _check(lib().tr_scene_ao_close_peers(self._h))
+
     def set_stream(self, cuda_stream):
         _check(lib().tr_scene_set_stream(self._h, ctypes.c_void_p(cuda_stream)))
 
