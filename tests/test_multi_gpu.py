@@ -40,6 +40,10 @@ def test_ao_peer_reduction_matches_nccl_and_single_gpu(world):
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
     out = json.loads(line)
+    scratch = os.path.join(ROOT, "gpurun_out")             # kept when run under gpurun (timings of the two exchanges)
+    if os.path.isdir(scratch):
+        with open(os.path.join(scratch, "ao_peer_check_n%d.json" % world), "w") as f:
+            f.write(line + "\n")
     assert out["ok"] and out["world"] == world
     assert all(c["identical_on_all_ranks"] for c in out["cases"])
 
