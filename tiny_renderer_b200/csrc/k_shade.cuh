@@ -99,10 +99,11 @@ __device__ __forceinline__ float shadow_lookup(const float* shadow, f3 s, uint32
     return __ldg(&shadow[min(idx, n_px)]);      // shadow[n_px] is a sentinel holding the cleared value (f32::MIN)
 }
 
-#ifndef TR_AO_UNROLL
-#define TR_AO_UNROLL 4
+#ifndef TR_AO_GROUP
+#define TR_AO_GROUP 8
 #endif
-constexpr int kAoUnroll = TR_AO_UNROLL;
+constexpr int kAoGroup = TR_AO_GROUP;
+static_assert(16 % kAoGroup == 0, "sample groups");
 // Occlusion fragment (shader.rs:886-947) for a pixel whose depth z and world position wp = from_homogeneous(i_vpmv *
 // (px, py, z, 1)) are known; returns the gray level.
 __device__ __forceinline__ uint32_t occlusion_gray(const float* shadow, const Uniforms& u, int px, int py, float z, f3 wp, DiagLocal& dl) {
@@ -123,27 +124,48 @@ __device__ __forceinline__ uint32_t occlusion_gray(const float* shadow, const Un
     const float* sm = u.shadow.m;
     const float reach_a = fmaxf(fmaxf(fabsf(wp.x), fabsf(wp.y)), fabsf(wp.z));
     const float w_base = fabsf(((sm[12] * wp.x + sm[13] * wp.y) + sm[14] * wp.z) + sm[15]);
-    const float reach = 0.0204f * u.ao_w_rowsum + 0x1p-20f * (u.ao_w_rowsum * (reach_a + 0.03f) + fabsf(sm[15]));
+    const float span = reach_a + 0.03f;
+    const float reach = 0.0204f * u.ao_w_rowsum + 0x1p-20f * (u.ao_w_rowsum * span + fabsf(sm[15]));
+    // The same argument bounds the samples' homogeneous x and y around X(wp), Y(wp) (rows 0 and 1), hence their
+    // shadow-buffer coordinates: |x / w| <= (|X(wp)| + reach_x) / (|W(wp)| - reach).  When that stays below width - 1
+    // (height - 1 for y) the rounded, saturated index parts are at most width - 1 and height - 1 — negative
+    // coordinates saturate to 0, as in the reference — so no sample can wrap into the next row or leave the buffer,
+    // and the loop needs neither the two diagnostics counts nor the clamp to the sentinel element.
+    const float x_base = fabsf(((sm[0] * wp.x + sm[1] * wp.y) + sm[2] * wp.z) + sm[3]);
+    const float y_base = fabsf(((sm[4] * wp.x + sm[5] * wp.y) + sm[6] * wp.z) + sm[7]);
+    const float reach_x = 0.0204f * u.ao_x_rowsum + 0x1p-20f * (u.ao_x_rowsum * span + fabsf(sm[3]));
+    const float reach_y = 0.0204f * u.ao_y_rowsum + 0x1p-20f * (u.ao_y_rowsum * span + fabsf(sm[7]));
+    const float w_least = w_base - reach;
     const bool untested = reach_a <= 1024.0f && w_base >= 0x1p-60f && w_base <= 0x1p60f && reach <= 0.5f * w_base &&
+                          x_base + reach_x <= (float)(u.width - 1u) * w_least && y_base + reach_y <= (float)(u.height - 1u) * w_least &&
                           (u.debug_flags & 1u) == 0u;
     auto samples = [&](auto untested_c) {
         constexpr bool UNTESTED = decltype(untested_c)::value;
-#pragma unroll kAoUnroll
-        for (int k = 0; k < 16; ++k) {
-            f3 sp = wp + u.ao_step[k];
-            const f4 sh = xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f});
-            f3 sc;
-            if (UNTESTED) {
-                const SharedDivisor d = shared_divisor(sh.w);
-                sc = {quotient(sh.x, d), quotient(sh.y, d), 0.0f};          // z of the sample is not used
-            } else {
-                sc = dehomog_shared(sh, ok);
-                count_if_zero(dl.w_zero, sh.w);
+        // Groups of kAoGroup samples: all shadow-buffer gathers of a group are issued before the first one is used.
+        // The untested form is unrolled completely, so the 16 steps are constant-bank operands of the additions.
+#pragma unroll (UNTESTED ? 16 / kAoGroup : 1)
+        for (int k0 = 0; k0 < 16; k0 += kAoGroup) {
+            float sv[kAoGroup];
+#pragma unroll
+            for (int j = 0; j < kAoGroup; ++j) {
+                f3 sp = wp + u.ao_step[k0 + j];
+                const f4 sh = xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f});
+                if (UNTESTED) {
+                    const SharedDivisor d = shared_divisor(sh.w);
+                    // z of the sample is not used
+                    sv[j] = __ldg(&shadow[round_u32(quotient(sh.x, d)) + round_u32(quotient(sh.y, d)) * u.width]);
+                } else {
+                    f3 sc = dehomog_shared(sh, ok);
+                    count_if_zero(dl.w_zero, sh.w);
+                    sv[j] = shadow_lookup(shadow, sc, u.width, n_px, dl);
+                }
             }
-            float sv = shadow_lookup(shadow, sc, u.width, n_px, dl);
-            if (sv - 1.0f > fsv) {
-                float strength = fminf(quotient(sv - fsv, d20), 1.0f);
-                occ -= 0.0625f * strength;
+#pragma unroll
+            for (int j = 0; j < kAoGroup; ++j) {
+                if (sv[j] - 1.0f > fsv) {
+                    float strength = fminf(quotient(sv[j] - fsv, d20), 1.0f);
+                    occ = __fmaf_rn(-0.0625f, strength, occ);       // occ -= 0.0625 * strength: the product is exact
+                }
             }
         }
     };
@@ -288,7 +310,10 @@ __global__ void __launch_bounds__(kShadeThreads) k_ao_compact(const ShadeArgs a,
     }
 }
 
-__global__ void __launch_bounds__(kShadeThreads) k_ao_accumulate(const ShadeArgs a, const Uniforms u, const AoList in, uint32_t n) {
+#ifndef TR_AO_MIN_CTAS
+#define TR_AO_MIN_CTAS 6      // 40 registers; measured best with groups of 8 (tools/tune_ao.sh)
+#endif
+__global__ void __launch_bounds__(kShadeThreads, TR_AO_MIN_CTAS) k_ao_accumulate(const ShadeArgs a, const Uniforms u, const AoList in, uint32_t n) {
     const uint32_t i = blockIdx.x * kShadeThreads + threadIdx.x;
     if (i >= n) return;
     const float4 frag = __ldg(&in.frag[i]);

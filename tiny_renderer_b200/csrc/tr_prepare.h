@@ -116,6 +116,8 @@ inline int prepare_camera_with_shadow(Uniforms& u, uint32_t width, uint32_t heig
     if (!invert4(u.m, &u.i_m)) return PREP_SINGULAR;
     u.shadow_from_screen = matmul(u.shadow, u.i_vpmv);
     u.ao_w_rowsum = (std::fabs(u.shadow.m[12]) + std::fabs(u.shadow.m[13])) + std::fabs(u.shadow.m[14]);
+    u.ao_x_rowsum = (std::fabs(u.shadow.m[0]) + std::fabs(u.shadow.m[1])) + std::fabs(u.shadow.m[2]);
+    u.ao_y_rowsum = (std::fabs(u.shadow.m[4]) + std::fabs(u.shadow.m[5])) + std::fabs(u.shadow.m[6]);
     if (want_ao) {
         f4 l4 = xform(u.i_m, f4{u.t_light.x, u.t_light.y, u.t_light.z, 0.0f});
         if (!(l4.w == 0.0f)) return PREP_LIGHT_W;

@@ -28,6 +28,7 @@ struct Uniforms {
     f3 t_light;
     f3 ao_step[16];               // (rot * (sin a_k, 0, cos a_k)) * 0.02   (shader.rs:920-929)
     float ao_w_rowsum;            // |s30| + |s31| + |s32| of `shadow` (bounds how far a sample's w moves; k_shade.cuh)
+    float ao_x_rowsum, ao_y_rowsum;   // the same sums over rows 0 and 1 (bound the samples' shadow-buffer coordinates)
     uint32_t debug_flags;         // bit 0: occlusion samples always take the range-tested division
     uint32_t width, height;
     uint32_t n_triangles;
