@@ -199,20 +199,41 @@ def algorithmic_bytes(n_px, covered, n_tri, pipe):
     return {"K1_vertex_setup": k1, "K3_raster_visibility": k35, "frame": 19 * n_px + tex + k1}
 
 
-def ncu_traffic(pipe):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused tile kernel, from the committed
-    newest `ncu --set full` summary (profiles/r1?_traffic.json, written by tools/ncu_summary.py); None when absent."""
+def ncu_kernel_summary(want):
+    """Entry of the kernel whose name contains `want` in the committed newest `ncu --set full` summary
+    (profiles/r*_traffic.json, written by tools/ncu_summary.py: DRAM bytes, duration and warp instructions per launch);
+    None when absent."""
     import glob
     found = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))
     if not found:
         return None
-    p = found[-1]
-    want = "k_raster<%d>" % {"phong": 1, "darboux": 4}[pipe]
-    with open(p) as f:
+    with open(found[-1]) as f:
         for k, v in json.load(f).items():
             if want in k:
-                return v["dram_bytes_per_launch"]
+                return dict(v, source=os.path.basename(found[-1]))
     return None
+
+
+def ncu_traffic(pipe):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused tile kernel (None when not captured)."""
+    e = ncu_kernel_summary("k_raster<%d>" % {"phong": 1, "darboux": 4}[pipe])
+    return e["dram_bytes_per_launch"] if e else None
+
+
+def issue_roofline(kernels, us, n_sm, sm_mhz):
+    """The bound these kernels actually run against: one warp instruction per cycle per SM sub-partition, which for
+    FP32 work is also the FP32 pipe's rate (tools/probe/ffma2_probe.cu: scalar FMUL+FADD reaches 95 % of it, packed
+    FFMA2 is half rate).  Warp instructions per launch come from the committed ncu capture of the named kernels
+    (they do not depend on timing), `us` is measured live.  None when a kernel has no capture."""
+    entries = [ncu_kernel_summary(k) for k in kernels]
+    if any(e is None for e in entries) or not sm_mhz:
+        return None
+    instr = sum(e["warp_instructions"] for e in entries)
+    peak = n_sm * 4 * sm_mhz * 1e6
+    ach = instr / (us * 1e-6)
+    return {"bound": "issue (1 warp instruction / cycle / SM sub-partition = the FP32 pipe rate)", "kernels": kernels,
+            "warp_instructions": instr, "us": us, "achieved": ach / 1e9, "peak": peak / 1e9, "unit": "G warp instr/s",
+            "frac": ach / peak, "source": entries[0]["source"]}
 
 
 def batch_roofline(us_per_frame, n_px, covered, n_tri, peak):
@@ -225,7 +246,7 @@ def batch_roofline(us_per_frame, n_px, covered, n_tri, peak):
 AO_LIGHTS = 1024
 
 
-def run_ao(args, rank, world, dev, model, dist, stream):
+def run_ao(args, rank, world, dev, model, dist, stream, sm_mhz=None):
     """BASELINE config 4: diablo, occlusion pipeline, 1024 light-direction depth passes at 3840x2160, lights sharded
     over the ranks (strong scaling: the light count is fixed), ONE sum of the u32 accumulators over the ranks at the
     end (the library's kernel over NVLink peer memory).  Device-timed (CUDA events on the launching stream), max over ranks."""
@@ -287,13 +308,15 @@ def run_ao(args, rank, world, dev, model, dist, stream):
     per_pass_bytes = 8 * n_px + 8 * covered              # shadow write + one read + u32 accumulate RMW
     peak, _ = load_peaks()
     us_per_pass = ms * 1e3 / max(1, hi - lo)
+    n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+    issue = issue_roofline(["k_raster<(int)-2>", "k_ao_accumulate"], us_per_pass, n_sm, sm_mhz) if rank == 0 else None
     return {"metric": "AO depth passes/s", "value": AO_LIGHTS / (ms * 1e-3), "unit": "passes/s", "n_gpus": world,
             "scaling": "strong", "lights": AO_LIGHTS, "lights_per_gpu": hi - lo, "ms": ms, "exchange": "k_ao_reduce_peers (own kernel, NVLink peer memory)" if world > 1 else "none",
             "exchange_ms": ar_ms, "nccl_allreduce_ms": nccl_ms, "exchange_bytes": 4 * n_px, "us_per_pass": us_per_pass, "checksum": int(total.astype(np.uint64).sum()),
             "shadow_index_oob": diag["shadow_index_oob"], "shadow_x_wrap": diag["shadow_x_wrap"],
             "roofline": {"bound": "hbm", "algorithmic_bytes_per_pass": per_pass_bytes,
                          "achieved": per_pass_bytes / (us_per_pass * 1e-6) / 1e9, "peak": peak,
-                         "frac": per_pass_bytes / (us_per_pass * 1e-6) / 1e9 / peak},
+                         "frac": per_pass_bytes / (us_per_pass * 1e-6) / 1e9 / peak, "issue": issue},
             "config": "BASELINE config 4: diablo, occlusion, %d light directions (SplitMix64 seed 0x5EED0A0, %d drawn), "
                       "3840x2160, camera angle 0" % (AO_LIGHTS, drawn)}
 
@@ -419,6 +442,24 @@ def run_gpu(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     e2e_value = world * e2e_steps * frames_per_step * n_px / e2e_s / 1e6
+    # What bounds e2e: the device->host link.  A plain cudaMemcpyAsync of one step's frame bytes into pinned memory,
+    # timed the same way, is the yardstick (rank 0, single-GPU runs only: ranks of one box share the host's link).
+    pcie = None
+    if rank == 0 and world == 1:
+        nbytes = frames_per_step * n_px * 3
+        src = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        dst = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+        dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        copy_s = (time.perf_counter() - t0) / 3
+        del src, dst
+        pcie = {"bound": "pcie d2h", "achieved": nbytes * e2e_steps / e2e_s / 1e9, "peak": nbytes / copy_s / 1e9, "unit": "GB/s",
+                "frac": (nbytes * e2e_steps / e2e_s) / (nbytes / copy_s),
+                "peak_source": "plain pinned device->host copy of one step's frame bytes, measured in this run"}
 
     line = {"metric": METRIC, "value": value, "unit": "Mpixels/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
@@ -428,7 +469,7 @@ def run_gpu(args, rank, world, local_rank):
                     "note": "tr_scene_render_views(views, frames -> pinned host): per frame clear/set_light_direction/set_camera/"
                             "render + device->host copy of the RGB8 frame, all inside the timed region; inputs are the 12 "
                             "floats of camera+light per frame (kernel arguments); PCIe-bound: 24.9 MB per frame",
-                    "host_numa_node": numa_node},
+                    "host_numa_node": numa_node, "roofline": pcie},
             "gpu_launches": int(launches), "clocks": clocks}
 
     if rank == 0:
@@ -468,6 +509,11 @@ def run_gpu(args, rank, world, local_rank):
                                              "achieved": frame_bytes / (frame_us * 1e-6) / 1e9,
                                              "frac": frame_bytes / (frame_us * 1e-6) / 1e9 / peak},
                             "batch": batch_roofline(ms / args.steps / frames_per_step * 1e3, n_px, covered, n_tri, peak)}
+        n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+        # the same kernel and the whole overlapped batch against the instruction-issue / FP32 rate (what actually binds them)
+        line["roofline"]["issue"] = issue_roofline(["k_raster<%d>" % {"phong": 1, "darboux": 4}[p]], us, n_sm, clocks.get("sm_mhz"))
+        line["roofline"]["batch"]["issue"] = issue_roofline(["k_raster<1>", "k_raster<4>", "k_vertex_setup<0>", "k_vertex_setup<0>"],
+                                                            2 * ms / args.steps / frames_per_step * 1e3, n_sm, clocks.get("sm_mhz"))
         if world == 1:
             # what a rasteriser resolving visibility with global 64-bit atomicMin could reach on this box
             # (distinct addresses, every atomic updates, one atomic per fragment); k_raster resolves in registers instead
@@ -478,7 +524,7 @@ def run_gpu(args, rank, world, local_rank):
             line["cpu_baseline"] = cpu_baseline(model)
     for s in scenes.values():
         s.close()
-    line["ao"] = run_ao(args, rank, world, dev, model, dist, stream)
+    line["ao"] = run_ao(args, rank, world, dev, model, dist, stream, sm_mhz=(clocks or {}).get("sm_mhz") if rank == 0 else None)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:
