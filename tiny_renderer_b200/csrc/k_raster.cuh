@@ -116,10 +116,8 @@ __device__ __forceinline__ uint32_t edge_block_mask(int4 e, int4 f) {
 
 // Stage polygon t into slot: edge equations relative to the tile origin, or raw coordinates when inexact.  s_mask /
 // s_maskx receive the blocks its bounding box overlaps (exact path / literal path; the other one is 0).
-__device__ __forceinline__ void stage_polygon(const RasterArgs& a, uint32_t t, int4 bb, int slot, int tx0, int ty0, int tx1, int ty1,
+__device__ __forceinline__ void stage_polygon(uint32_t t, int4 bb, float4 r0, float4 r1, float4 r2, int slot, int tx0, int ty0, int tx1, int ty1,
                                               float* s_tri, uint32_t* s_mask, uint32_t* s_maskx, int* s_inexact) {
-    const float4* r = a.rec + (size_t)t * 4;
-    float4 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
     int x0 = __float_as_int(r0.x), y0 = __float_as_int(r0.y), x1 = __float_as_int(r0.z), y1 = __float_as_int(r0.w);
     int x2 = __float_as_int(r1.x), y2 = __float_as_int(r1.y);
     long long ex = (long long)max(max(x0, x1), x2) - min(min(x0, x1), x2), ey = (long long)max(max(y0, y1), y2) - min(min(y0, y1), y2);
@@ -196,6 +194,13 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
 
     const uint32_t cell = (uint32_t)(ty0 / kCellH) * a.bins.cells_x + (uint32_t)(tx0 / kCellW);
     const uint32_t n_bin = a.bins.count[a.bins.parity * a.bins.n_cells + cell];
+    // The filter below is a chain of dependent loads (bin count -> list entry -> bounding box -> setup record) that
+    // the whole CTA waits for.  The first list entry of every thread is fetched alongside the count (the slot exists
+    // whatever the count says; it is only used when it turns out to be valid), and a polygon's bounding box and
+    // record travel together, so the chain is two loads deep instead of four.
+#ifndef TR_NO_FILTER_PREFETCH
+    const uint32_t t_first = a.bins.list[(size_t)cell * kBinCap + tid];
+#endif
     const bool cleared = a.fresh || (!DEPTH_ONLY && a.tile_state[tile] != 0u);
     // With a cleared frame the tile's RGB is rebuilt completely (zeros where nothing is drawn) and stored in bulk.
     const bool rgb_bulk = SHADE && sa.fresh;
@@ -224,18 +229,30 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
             uint32_t i = base + lane, t = 0;
             bool hit = false;
             int4 bb = make_int4(1, 0, 0, 0);
+            float4 r0 = make_float4(0.0f, 0.0f, 0.0f, 0.0f), r1 = r0, r2 = r0;
             if (i < n_src) {
+#ifndef TR_NO_FILTER_PREFETCH
+                t = !use_bin ? i : (i == (uint32_t)tid ? t_first : a.bins.list[(size_t)cell * kBinCap + i]);
+#else
                 t = use_bin ? a.bins.list[(size_t)cell * kBinCap + i] : i;
+#endif
                 bb = __ldg(&a.bbox[t]);
+#ifndef TR_NO_FILTER_PREFETCH
+                const float4* r = a.rec + (size_t)t * 4;
+                r0 = __ldg(r); r1 = __ldg(r + 1); r2 = __ldg(r + 2);
+#endif
                 hit = bb.x <= bb.z && bb.x <= tx1 && bb.z >= tx0 && bb.y <= ty1 && bb.w >= ty0;
             }
+#ifdef TR_NO_FILTER_PREFETCH
+            if (hit) { const float4* r = a.rec + (size_t)t * 4; r0 = __ldg(r); r1 = __ldg(r + 1); r2 = __ldg(r + 2); }
+#endif
             const unsigned m = __ballot_sync(0xffffffffu, hit);
             if (m == 0u) continue;
             int first = 0;
             if (lane == 0) first = atomicAdd(&s_count, __popc(m));
             first = __shfl_sync(0xffffffffu, first, 0);
             const int slot = first + __popc(m & ((1u << lane) - 1u));
-            if (hit && slot < kListCap) stage_polygon(a, t, bb, slot, tx0, ty0, tx1, ty1, s_tri, s_mask, s_maskx, &s_inexact);
+            if (hit && slot < kListCap) stage_polygon(t, bb, r0, r1, r2, slot, tx0, ty0, tx1, ty1, s_tri, s_mask, s_maskx, &s_inexact);
             if (hit && slot >= kListCap) atomicMin(&s_next, (int)i);       // a source entry that did not fit
         }
         __syncthreads();
