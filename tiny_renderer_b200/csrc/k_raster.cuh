@@ -29,19 +29,38 @@
 
 namespace tr {
 
-#ifdef TR_MIN_CTAS
-#define TR_RASTER_BOUNDS __launch_bounds__(kRasterThreads, TR_MIN_CTAS)
-#else
-// Residency measured best (A/B in profiles/README.md): 6 CTAs per SM (40 registers, no spills; also the shared-memory
-// limit) for every instantiation but darboux, whose fragment code spills below 64 registers and is held to 4.
+// Two CTA shapes of the same kernel (template parameter THREADS, measured in profiles/README.md):
+//   * 256 threads, 512-polygon lists, 6 CTAs per SM (40 registers, no spills; also the shared-memory limit; darboux,
+//     whose fragment code spills below 64 registers: 4) — a lone frame: the heavy tiles set the frame's duration, and
+//     eight warps finish one sooner than four;
+//   * 128 threads, 192-polygon lists, 12 CTAs per SM (darboux: 8) — overlapped batches (view batches, the many-light
+//     AO batch): the same number of resident warps in smaller barrier groups, and a tile's ragged tail idles four
+//     warps instead of eight; the longer tiles no longer matter because the next frame's work fills in behind them.
 #ifndef TR_MIN_CTAS_LIGHT
 #define TR_MIN_CTAS_LIGHT 6
 #endif
 #ifndef TR_MIN_CTAS_DARBOUX
 #define TR_MIN_CTAS_DARBOUX 4
 #endif
-#define TR_RASTER_BOUNDS __launch_bounds__(kRasterThreads, MODE == P_DARBOUX ? TR_MIN_CTAS_DARBOUX : TR_MIN_CTAS_LIGHT)
+#ifndef TR_RASTER_THREADS_BATCH
+#define TR_RASTER_THREADS_BATCH 128
 #endif
+#ifndef TR_LIST_CAP_BATCH
+#define TR_LIST_CAP_BATCH 192
+#endif
+#ifndef TR_MIN_CTAS_LIGHT_BATCH
+#define TR_MIN_CTAS_LIGHT_BATCH 12
+#endif
+#ifndef TR_MIN_CTAS_DARBOUX_BATCH
+#define TR_MIN_CTAS_DARBOUX_BATCH 8
+#endif
+constexpr int kRasterThreadsBatch = TR_RASTER_THREADS_BATCH;
+__host__ __device__ constexpr int raster_list_cap(int threads) { return threads == kRasterThreads ? kListCap : TR_LIST_CAP_BATCH; }
+__host__ __device__ constexpr int raster_min_ctas(int threads, bool darboux) {
+    return threads == kRasterThreads ? (darboux ? TR_MIN_CTAS_DARBOUX : TR_MIN_CTAS_LIGHT)
+                                     : (darboux ? TR_MIN_CTAS_DARBOUX_BATCH : TR_MIN_CTAS_LIGHT_BATCH);
+}
+#define TR_RASTER_BOUNDS __launch_bounds__(THREADS, raster_min_ctas(THREADS, MODE == P_DARBOUX))
 #ifndef TR_PIXELS_PER_LANE
 #define TR_PIXELS_PER_LANE 2
 #endif
@@ -167,14 +186,15 @@ __device__ __noinline__ BlockState load_block_state(const unsigned long long* ke
     return st;
 }
 
-template <int MODE>
+template <int MODE, int THREADS>
 __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u, const __grid_constant__ CUtensorMap rgb_map,
                                          const __grid_constant__ CUtensorMap rgb_map_top) {
     constexpr bool DEPTH_ONLY = MODE == kModeDepthOnly;
     constexpr bool SHADE = MODE >= 0;
     constexpr int kRgbRow = kTileW * 3;
-    __shared__ __align__(16) float s_tri[kListCap * kStageWords];
-    __shared__ uint32_t s_mask[kListCap], s_maskx[kListCap];   // per staged polygon: blocks to visit (exact / literal path)
+    constexpr int kThreads = THREADS, kCap = raster_list_cap(THREADS);
+    __shared__ __align__(16) float s_tri[kCap * kStageWords];
+    __shared__ uint32_t s_mask[kCap], s_maskx[kCap];   // per staged polygon: blocks to visit (exact / literal path)
     // the tile's RGB in frame order (top-down: tile row r at s_rgb row rows-1-r, rows = the tile's on-screen rows), the
     // box of the TMA store
     __shared__ __align__(128) uint8_t s_rgb[SHADE ? kTileH * kRgbRow : 16];
@@ -215,7 +235,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     uint32_t scan_from = 0;
     bool more = n_src > 0;
     while (more) {
-        // ---- (1) filter the source list (cell bin, or all polygons) against the tile, kListCap polygons per round ----
+        // ---- (1) filter the source list (cell bin, or all polygons) against the tile, kCap polygons per round ----
         if (tid == 0) { s_count = 0; s_next = (int)n_src; s_block = 0; s_inexact = 0; }
         __syncthreads();
         // Warps walk the list independently (no barrier per step): a warp ballots its 32 entries, reserves slots for
@@ -224,8 +244,8 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         // list overflows, s_next ends up at the smallest source index that was not staged and the next round restarts
         // there; entries beyond it that did get a slot are staged again, which changes nothing (an equal key never
         // beats itself).
-        for (uint32_t base = scan_from + warp * 32; base < n_src; base += kRasterThreads) {
-            if (*(volatile int*)&s_count >= kListCap) { if (lane == 0) atomicMin(&s_next, (int)base); break; }
+        for (uint32_t base = scan_from + warp * 32; base < n_src; base += kThreads) {
+            if (*(volatile int*)&s_count >= kCap) { if (lane == 0) atomicMin(&s_next, (int)base); break; }
             uint32_t i = base + lane, t = 0;
             bool hit = false;
             int4 bb = make_int4(1, 0, 0, 0);
@@ -252,11 +272,11 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
             if (lane == 0) first = atomicAdd(&s_count, __popc(m));
             first = __shfl_sync(0xffffffffu, first, 0);
             const int slot = first + __popc(m & ((1u << lane) - 1u));
-            if (hit && slot < kListCap) stage_polygon(t, bb, r0, r1, r2, slot, tx0, ty0, tx1, ty1, s_tri, s_mask, s_maskx, &s_inexact);
-            if (hit && slot >= kListCap) atomicMin(&s_next, (int)i);       // a source entry that did not fit
+            if (hit && slot < kCap) stage_polygon(t, bb, r0, r1, r2, slot, tx0, ty0, tx1, ty1, s_tri, s_mask, s_maskx, &s_inexact);
+            if (hit && slot >= kCap) atomicMin(&s_next, (int)i);       // a source entry that did not fit
         }
         __syncthreads();
-        const int n_list = min(s_count, kListCap);
+        const int n_list = min(s_count, kCap);
         const int n_inexact = s_inexact;
         scan_from = (uint32_t)s_next;       // == n_src when everything was staged
         more = scan_from < n_src;
@@ -264,7 +284,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         touched = true;
         // Narrow the bounding-box masks of the exact-path polygons to the blocks the triangle itself reaches (one lane
         // per staged polygon), and pad both mask arrays with zeros to a whole warp for the sweeps below.
-        for (int i = tid; i < ((n_list + 31) & ~31); i += kRasterThreads) {
+        for (int i = tid; i < ((n_list + 31) & ~31); i += kThreads) {
             if (i >= n_list) { s_mask[i] = 0u; s_maskx[i] = 0u; continue; }
             const uint32_t m = s_mask[i];
             if (m) {
@@ -277,7 +297,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         // ---- (2) warps pull 8 x (4*kPix) blocks off the tile (a lane owns kPix pixels, 4 rows apart); ballot the staged
         //      bboxes against the block, evaluate per pixel ----
 #ifdef TR_STATIC_BLOCKS
-        for (int blk = warp; blk < kBlocks; blk += kRasterThreads / 32) {
+        for (int blk = warp; blk < kBlocks; blk += kThreads / 32) {
 #else
         for (;;) {
             // (the assembler wraps an atomic add in a ~15-instruction warp-aggregation sequence even for one lane; the
@@ -420,10 +440,10 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
                     const float4 v = make_float4(kFloatMin, kFloatMin, kFloatMin, kFloatMin);
                     const int c = tid % (kTileW / 4);
                     if (c < quads)
-                        for (int r = tid / (kTileW / 4); r <= ty1 - ty0; r += kRasterThreads / (kTileW / 4))
+                        for (int r = tid / (kTileW / 4); r <= ty1 - ty0; r += kThreads / (kTileW / 4))
                             reinterpret_cast<float4*>(a.depth + (size_t)(ty0 + r) * a.width + tx0)[c] = v;
                 } else {
-                    for (int i = tid; i < kTileW * kTileH; i += kRasterThreads) {
+                    for (int i = tid; i < kTileW * kTileH; i += kThreads) {
                         int px = tx0 + i % kTileW, py = ty0 + i / kTileW;
                         if (px < (int)a.width && py < (int)a.height) a.depth[(size_t)py * a.width + px] = kFloatMin;
                     }
@@ -442,7 +462,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         //      hardware).  A tile nothing touches is all zeros; when it already was, nothing is written at all.
         if (!touched && sa.rgb_zero[tile] != 0u) return;
         if (!touched) {
-            for (int i = tid; i < kTileH * kRgbRow / 16; i += kRasterThreads) reinterpret_cast<uint4*>(s_rgb)[i] = make_uint4(0u, 0u, 0u, 0u);
+            for (int i = tid; i < kTileH * kRgbRow / 16; i += kThreads) reinterpret_cast<uint4*>(s_rgb)[i] = make_uint4(0u, 0u, 0u, 0u);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncthreads();
         }
@@ -461,7 +481,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
                 asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             }
         } else {
-            for (int i = tid; i < rows * row_bytes; i += kRasterThreads) {
+            for (int i = tid; i < rows * row_bytes; i += kThreads) {
                 int r = i / row_bytes, c = i % row_bytes;
                 sa.rgb[((size_t)(a.height - 1 - (ty0 + r)) * a.width + tx0) * 3 + c] = s_rgb[(rows - 1 - r) * kRgbRow + c];
             }

@@ -421,7 +421,9 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     a.tile_order = s->tile_order + (s->overlapping ? (size_t)s->tiles_x * s->tiles_y : 0);
     dim3 grid(s->tiles_x * s->tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
-#define TR_RASTER(M) k_raster<M><<<grid, kRasterThreads, 0, s->stream>>>(a, sa, u, S(s).rgb_map, S(s).rgb_map_top)
+    // CTA shape: 256 threads for a lone frame, 128 for overlapped batches (k_raster.cuh)
+#define TR_RASTER(M) do { if (s->overlapping) k_raster<M, kRasterThreadsBatch><<<grid, kRasterThreadsBatch, 0, s->stream>>>(a, sa, u, S(s).rgb_map, S(s).rgb_map_top); \
+                          else k_raster<M, kRasterThreads><<<grid, kRasterThreads, 0, s->stream>>>(a, sa, u, S(s).rgb_map, S(s).rgb_map_top); } while (0)
     switch (mode) {
         case kModeDepthOnly: TR_RASTER(kModeDepthOnly); break;
         case kModeVisibility: TR_RASTER(kModeVisibility); break;
