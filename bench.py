@@ -32,6 +32,7 @@ METRIC = "Mpixels/s shaded (device-timed) at 3840x2160"
 PIPES = ("phong", "darboux")
 N_ANGLES = 8
 LIGHT_ANGLE = 0.7
+PREROLL_STEPS = 2   # untimed steps queued directly in front of the timed ones (see run_gpu)
 RING = int(os.environ.get("TINYR_RING", "8"))   # frame slots per scene: 8 x (8 B keys + 3 B rgb) x 8.29 Mpx = 730 MB of render targets > 126 MB L2
 
 
@@ -180,7 +181,8 @@ def workload_config():
                         "(16 frames per step per GPU)", "width": W4K, "height": H4K, "frames_per_step_per_gpu": len(PIPES) * N_ANGLES,
             "triangles": 5022, "l2": "render targets rotate through a ring of %d buffer sets per scene (%d MB of keys + RGB > 126 MB L2)" % (RING, RING * W4K * H4K * 11 // 1000000),
             "parallelism": "independent view batches per GPU, no data-path collective; on a GPU the phong scene and the "
-                           "darboux scene run on a stream each, frames of a scene overlap on its %d frame slots" % RING}
+                           "darboux scene run on a stream each, frames of a scene overlap on its %d frame slots" % RING,
+            "preroll_steps": PREROLL_STEPS}
 
 
 # ---- GPU arm -----------------------------------------------------------------------------------------------
@@ -402,11 +404,18 @@ def run_gpu(args, rank, world, local_rank):
         step()
     for s in scenes.values():
         s.kernel_times()                      # reset launch counters
-    sampler = ClockSampler(dev)
-    if rank == 0:
-        sampler.start()
+    sampler = ClockSampler(dev)          # every rank samples its own GPU: `value` is set by the slowest one
+    sampler.start()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # Two more untimed steps behind the barrier, joined before e0: the device has drained them when the timed steps
+    # start, but the host has long since queued the timed steps behind them.  Without this the first timed launches
+    # are fed by a host thread that has just left the barrier; with 8 ranks on one host a single late wake-up showed
+    # up as 10 % of a 20-step (9 ms) region on one rank — and `value` is the slowest rank's.
+    fork()
+    for _ in range(PREROLL_STEPS):
+        step()
+    join()
     e0.record()
     fork()
     for _ in range(args.steps):
@@ -415,12 +424,17 @@ def run_gpu(args, rank, world, local_rank):
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop()
     launches = sum(n for s in scenes.values() for (_, n) in s.kernel_times().values())
     if dist is not None:
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, {"rank": rank, "ms_per_step": ms / args.steps, "sm_mhz": clocks["sm_mhz"], "reasons": clocks["reasons"]})
         t = torch.tensor([ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
+        # the line's clocks describe the whole job: lowest median clock and every throttle reason any rank saw
+        mhz = [r["sm_mhz"] for r in per_rank if r["sm_mhz"]]
+        clocks = dict(clocks, sm_mhz=min(mhz) if mhz else None, reasons=sorted({x for r in per_rank for x in r["reasons"]}), per_rank=per_rank)
     frames_per_step = len(PIPES) * N_ANGLES
     value = world * args.steps * frames_per_step * n_px / (ms * 1e-3) / 1e6
 

@@ -95,6 +95,28 @@ def test_render_views_two_pass_pipeline_overlapped(tinyr, oracle):
     g.close()
 
 
+@pytest.mark.parametrize("pipeline", ["darboux", "shadow"])
+def test_batch_shape_of_the_tile_kernel_with_long_polygon_lists(tinyr, oracle, pipeline):
+    """Overlapped batches run the tile kernel in its 128-thread shape, whose staged list holds 192 polygons: with
+    the whole model inside a handful of tiles every tile needs many rounds (overflowed bins scan all polygons, later
+    rounds merge with the winners of the earlier ones, the fragment stage re-derives barycentrics for winners of an
+    earlier round).  Every frame of the batch equals the oracle's; sizes with partial tiles."""
+    from tiny_renderer_b200.scene import Scene
+    m = get_model("diablo")
+    w, h = 150, 70
+    views = turntable(5, light_angle=1.3, phase=0.2)
+    g = Scene(w, h, m, pipeline, ring=3)
+    frames = np.zeros((5, h, w, 3), np.uint8)
+    g.render_views(views, want_checksums=False, frames_out=frames)
+    vis_last = g.raw_visibility()
+    for k in range(5):
+        o = oracle.OracleScene(w, h, m, pipeline)
+        parity.drive(o, views[k, 0:3], views[k, 3:6], views[k, 6:9], views[k, 9:12])
+        assert np.array_equal(frames[k], o.get_frame_buffer()), k
+    assert np.array_equal(vis_last, o.raw_visibility())
+    g.close()
+
+
 @pytest.mark.parametrize("ring", [1, 3])
 def test_ao_batch_matches_oracle_and_is_shard_invariant(tinyr, oracle, ring):
     """Config 4 semantics at test size: accum = sum over lights of the occlusion gray frame (u32).  GPU == oracle
