@@ -1,5 +1,7 @@
 #!/bin/bash
-# Rebuilds libtinyr.so with different tile shapes / CTA sizes on the GPU box and prints the bench numbers.
+# Rebuilds libtinyr.so with different tile shapes / CTA sizes (of the lone-frame shape; the batch shape has its own
+# -DTR_RASTER_THREADS_BATCH / -DTR_LIST_CAP_BATCH / -DTR_MIN_CTAS_*_BATCH knobs, see tools/tune_ao.sh) on the GPU box and
+# prints the bench numbers.
 # usage (under gpurun): bash tools/tune_raster.sh "256 64 32" "512 64 32" ...
 set -u
 cd "$(dirname "$0")/.."
