@@ -147,3 +147,20 @@ def test_cli_usage_and_missing_assets(tinyr):
     assert out.returncode == 0 and "-p asset_dir" in out.stdout and "true_normal" in out.stdout
     out = subprocess.run([tinyr.CLI_PATH, "-p", "/nonexistent", "-s", "phong", "--out", "/tmp/none.tga"], capture_output=True, text=True)
     assert out.returncode == 1 and "TR_ERR" not in out.stdout and "model.obj" in (out.stderr + out.stdout)
+
+
+def test_bench_finds_the_committed_ncu_summaries():
+    """bench.py fills roofline.traffic and the issue-rate rooflines from the newest profiles/r*_traffic.json; a kernel
+    renamed without a fresh capture would silently turn them into nulls."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_under_test", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    for want in ("k_raster<1,256>", "k_raster<4,256>", "k_raster<1,128>", "k_raster<4,128>", "k_raster<-2,128>",
+                 "k_ao_accumulate", "k_vertex_setup<0>"):
+        e = bench.ncu_kernel_summary(want)
+        assert e is not None and e["warp_instructions"] > 0 and e["dram_bytes_per_launch"] > 0, want
+    assert bench.ncu_traffic("darboux") > bench.ncu_traffic("phong") > 0
+    r = bench.issue_roofline(["k_raster<-2,128>", "k_ao_accumulate"], 56.6, 148, 1965.0)
+    assert 0.5 < r["frac"] < 1.0 and abs(r["peak"] - 148 * 4 * 1.965) < 1e-6
+    assert bench.issue_roofline(["no_such_kernel"], 10.0, 148, 1965.0) is None
