@@ -213,6 +213,9 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     const float kFloatMin = -3.402823466e38f;
 
     const uint32_t cell = (uint32_t)(ty0 / kCellH) * a.bins.cells_x + (uint32_t)(tx0 / kCellW);
+    // Everything above only reads launch-time constants (the tile order table is written at scene creation); from here
+    // on the kernel reads what the vertex set-up kernel in front of it wrote (tinyr.cu: launch_raster).
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const uint32_t n_bin = a.bins.count[a.bins.parity * a.bins.n_cells + cell];
     // The filter below is a chain of dependent loads (bin count -> list entry -> bounding box -> setup record) that
     // the whole CTA waits for.  The first list entry of every thread is fetched alongside the count (the slot exists

@@ -29,6 +29,9 @@ __device__ __forceinline__ f3 normal_to_camera(const Uniforms& u, f3 n, unsigned
 template <bool LIGHT_PASS>
 __global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__ geom, SetupOut out, const Uniforms u,
                                                      int pipeline, unsigned long long* diag) {
+    // The tile kernel behind this one is launched with programmatic stream serialization (tinyr.cu: launch_raster): let
+    // it start now; it waits for this grid's completion before it touches anything written here.
+    asm volatile("griddepcontrol.launch_dependents;");
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = t < u.n_triangles;        // no early return: the whole warp takes part in the binning
     if (!valid) t = u.n_triangles - 1;

@@ -405,6 +405,27 @@ ShadeArgs shade_args(tr_scene* s, bool fresh_rgb) {
     return a;
 }
 
+// The tile kernel is launched with programmatic stream serialization: it may start while the vertex set-up kernel in
+// front of it (which signals griddepcontrol.launch_dependents on entry) is still running, does everything that does
+// not depend on that kernel's output — tile coordinates, shared-memory set-up — and then waits (griddepcontrol.wait)
+// for its completion and memory flush.  For a lone frame this hides the tile kernel's launch latency behind K1.
+// TINYR_NO_PDL=1 in the environment restores plain launches (A/B in profiles/README.md).
+static const bool g_pdl = getenv("TINYR_NO_PDL") == nullptr;
+template <int M, int T>
+static void launch_raster(tr_scene* s, dim3 grid, const RasterArgs& a, const ShadeArgs& sa, const Uniforms& u) {
+    if (!g_pdl) {
+        k_raster<M, T><<<grid, T, 0, s->stream>>>(a, sa, u, S(s).rgb_map, S(s).rgb_map_top);
+        return;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = dim3(T); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, k_raster<M, T>, a, sa, u, S(s).rgb_map, S(s).rgb_map_top);
+}
+
 // mode: kModeDepthOnly (K4), kModeVisibility (K3 alone) or a pipeline id (K3 + K5 fused).
 int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms& u, bool fresh_rgb) {
     const bool depth_only = mode == kModeDepthOnly;
@@ -422,8 +443,8 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     dim3 grid(s->tiles_x * s->tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
     // CTA shape: 256 threads for a lone frame, 128 for overlapped batches (k_raster.cuh)
-#define TR_RASTER(M) do { if (s->overlapping) k_raster<M, kRasterThreadsBatch><<<grid, kRasterThreadsBatch, 0, s->stream>>>(a, sa, u, S(s).rgb_map, S(s).rgb_map_top); \
-                          else k_raster<M, kRasterThreads><<<grid, kRasterThreads, 0, s->stream>>>(a, sa, u, S(s).rgb_map, S(s).rgb_map_top); } while (0)
+#define TR_RASTER(M) do { if (s->overlapping) launch_raster<M, kRasterThreadsBatch>(s, grid, a, sa, u); \
+                          else launch_raster<M, kRasterThreads>(s, grid, a, sa, u); } while (0)
     switch (mode) {
         case kModeDepthOnly: TR_RASTER(kModeDepthOnly); break;
         case kModeVisibility: TR_RASTER(kModeVisibility); break;
