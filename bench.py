@@ -145,6 +145,25 @@ def cpu_baseline(model, n_frames_per_pipe=2):
                       % (len(jobs), n_frames_per_pipe, secs)}
 
 
+def cpu_ao_baseline(model, n_lights, threads):
+    """BASELINE config 4 on the host: per light the reference's sequence set_light_direction / clear / render with the
+    occlusion pipeline (both passes, shader.rs:806-963) at 3840x2160, camera angle 0 — what tr_scene_render_ao sums.  A
+    bounded sample of the 1,024 lights (the first n of the same seeded list), one light per host thread."""
+    import assets
+    import tiny_renderer_b200 as tr
+    lights, _ = tr.generate_ao_lights(model.positions, n_lights)
+    lf, la, up, _ = assets.view_vectors(0.0, 0.0)
+    jobs = []
+    for l in lights:
+        v = np.zeros(12, np.float32)
+        v[0:3], v[3:6], v[6:9], v[9:12] = lf, la, up, l
+        jobs.append(("occlusion", v))
+    secs = cpu_render_frames(model, jobs, threads)
+    return {"value": n_lights / secs, "unit": "passes/s", "cores": threads, "kind": "port",
+            "sample": "%d of the %d light directions at 3840x2160, oracle C++ port of the occlusion pipeline, %d thread%s, %.2f s"
+                      % (n_lights, AO_LIGHTS, threads, "" if threads == 1 else "s", secs)}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU implementation of the path (the oracle port — the Rust crate cannot
     be built on this box) on all host threads it can use, same config/metric/unit."""
@@ -173,6 +192,9 @@ def run_reference(args, rank, world):
                              "sample": "%d frames per step (%d views x phong+darboux) at 3840x2160, oracle C++ port of "
                                        "scene.rs/shader.rs, one frame per host thread, %d threads" % (len(jobs), sample_views, threads)},
             "e2e": {"value": value, "unit": "Mpixels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    # the second half of BASELINE's metric, once per run (not per step): one light per host thread
+    ao = cpu_ao_baseline(model, threads, threads)
+    line["ao"] = {"metric": "AO depth passes/s", "value": ao["value"], "unit": "passes/s", "cpu_baseline": ao}
     print(json.dumps(line), flush=True)
 
 
@@ -543,9 +565,12 @@ def run_gpu(args, rank, world, local_rank):
                                        "us_per_4k_depth_layer": n_px / rate * 1e6,
                                        "note": "micro-benchmark only (tr_bench_atomic_min); not on the render path"}
             line["cpu_baseline"] = cpu_baseline(model)
+            ao_cpu = cpu_ao_baseline(model, 3, 1)
     for s in scenes.values():
         s.close()
     line["ao"] = run_ao(args, rank, world, dev, model, dist, stream, sm_mhz=(clocks or {}).get("sm_mhz") if rank == 0 else None)
+    if rank == 0 and world == 1:
+        line["ao"]["cpu_baseline"] = ao_cpu
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:
