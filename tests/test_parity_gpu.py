@@ -324,3 +324,58 @@ def test_fuzz_sequences_with_and_without_clear(tinyr, oracle, pipeline):
     assert np.array_equal(g.get_frame_buffer(), o.get_frame_buffer())
     assert np.array_equal(g.raw_z(), o.raw_z())
     g.close()
+
+
+def _tile_pile_model(n_in_tile, n_elsewhere, seed):
+    """Small front-facing triangles: n_in_tile of them strictly inside the bottom-left 64x32 tile of a 128x64 frame
+    (camera at +z looking at the origin), n_elsewhere strictly inside the tile to its right — the same binning cell,
+    so they are in the tile's source list but fail its bounding-box filter."""
+    from tiny_renderer_b200.scene import Model
+    m = get_model("african_head")
+    rng = np.random.default_rng(seed)
+    pos, tri = [], []
+    for k in range(n_in_tile + n_elsewhere):
+        left = k < n_in_tile
+        cx = rng.uniform(-0.9, -0.15) if left else rng.uniform(0.15, 0.9)
+        cy = rng.uniform(-0.9, -0.15)
+        z = rng.uniform(-0.5, 0.5)
+        r = rng.uniform(0.02, 0.08)
+        a = rng.uniform(0, 2 * math.pi)
+        v0 = len(pos)
+        for j in range(3):              # counter-clockwise seen from +z: front-facing
+            pos.append([cx + r * math.cos(a + 2.1 * j), cy + r * math.sin(a + 2.1 * j), z + 0.05 * j])
+        tri.append([v0, (7 * k) % len(m.uvs), k % len(m.normals), v0 + 1, (7 * k + 1) % len(m.uvs), (k + 1) % len(m.normals),
+                    v0 + 2, (7 * k + 2) % len(m.uvs), (k + 2) % len(m.normals)])
+    return Model(np.array(pos, np.float32), m.uvs, m.normals, np.array(tri, np.uint32), m.maps, "pile")
+
+
+@pytest.mark.parametrize("batch_shape", [False, True])
+def test_tile_list_exactly_full(tinyr, oracle, batch_shape):
+    """A tile whose polygon list fills the staged list EXACTLY (and 1 over, and twice): the round that fills the list
+    ends with `more` set, the next one stages nothing — the fragment stage must still run (k_raster.cuh: the empty
+    closing round).  Both CTA shapes: 256 threads / 512 entries (lone frame) and 128 threads / 192 entries (batch)."""
+    from tiny_renderer_b200.scene import Scene
+    cap = 192 if batch_shape else 512
+    lf, la, up, light = assets.view_vectors(0.0, 0.3)
+    for n_in, n_out in ((cap, 100), (cap + 1, 37), (2 * cap, 0), (cap, 0), (cap - 1, 300)):
+        model = _tile_pile_model(n_in, n_out, 1000 + n_in + n_out)
+        for pipeline in ("phong", "darboux"):
+            o = oracle.OracleScene(128, 64, model, pipeline)
+            parity.drive(o, lf, la, up, light)
+            vis = o.raw_visibility()
+            assert (vis[:32, :64] != 0xFFFFFFFF).sum() > 200 and (vis[32:, :] == 0xFFFFFFFF).all()
+            for rep in range(3):        # the staging order (hence which warp sees the list full) varies from run to run
+                if batch_shape:
+                    g = Scene(128, 64, model, pipeline, ring=2)
+                    v = np.zeros((2, 12), np.float32)
+                    v[:, 0:3], v[:, 3:6], v[:, 6:9], v[:, 9:12] = lf, la, up, light
+                    frames = np.zeros((2, 64, 128, 3), np.uint8)
+                    g.render_views(v, want_checksums=False, frames_out=frames)
+                    assert np.array_equal(frames[0], o.get_frame_buffer()), (n_in, n_out, pipeline, rep)
+                    assert np.array_equal(frames[1], o.get_frame_buffer()), (n_in, n_out, pipeline, rep)
+                else:
+                    g = Scene(128, 64, model, pipeline)
+                    parity.drive(g, lf, la, up, light)
+                st = parity.compare(g, o, rgb_frac=1.0)
+                assert st["rgb_exact_frac"] == 1.0 and st["depth_bits_differ"] == 0, (n_in, n_out, pipeline, rep, st)
+                g.close()

@@ -283,7 +283,12 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
         const int n_inexact = s_inexact;
         scan_from = (uint32_t)s_next;       // == n_src when everything was staged
         more = scan_from < n_src;
-        if (n_list == 0) break;             // (more is false here: a round that staged nothing reached the end)
+        // A round that staged nothing reached the end of the source list (more is false).  In the shading modes it still
+        // has to run when earlier rounds left winners behind: the fragment stage only runs in the last round, and the
+        // round before this one ended with `more` set (it filled the list exactly, or a warp saw the list full before it
+        // had looked at its remaining entries), so nothing has been shaded yet.  The block loop below then runs with an
+        // empty list: winners come from memory and their barycentrics are re-derived.
+        if (n_list == 0 && !(SHADE && touched)) break;
         touched = true;
         // Narrow the bounding-box masks of the exact-path polygons to the blocks the triangle itself reaches (one lane
         // per staged polygon), and pad both mask arrays with zeros to a whole warp for the sweeps below.
