@@ -108,7 +108,9 @@ int tr_scene_render_views(tr_scene* s, const tr_view* views, uint32_t n_views, u
 /* Many-light ambient occlusion: for each light `set_light_direction; clear; render` with the occlusion
  * pipeline (shader.rs:806-963) and accum[i + j*w] += gray (u32).  Camera visibility is computed once.
  * The sums stay on the device (tr_scene_ao_device_buffer); accum_host (optional) receives a copy.
- * reset != 0 zeroes the accumulator first. */
+ * reset != 0 zeroes the accumulator first.  Afterwards the shadow-buffer getters show the depth pass of ONE of the
+ * lights (the last one with ring == 1; with ring > 1 whichever pass ran last on the camera's slot, or the earlier
+ * contents when none did): they are a debug view, not part of the batch's result. */
 int tr_scene_render_ao(tr_scene* s, const float* light_dirs_xyz, uint32_t n_lights, int reset, uint32_t* accum_host);
 int tr_scene_ao_device_buffer(tr_scene* s, void** device_ptr_u32, size_t* n_elements);
 int tr_scene_read_ao(tr_scene* s, uint32_t* accum_host);
@@ -140,8 +142,9 @@ int tr_ao_generate_lights(const float* positions_xyz, uint32_t n_positions, cons
 int tr_device_count(int* n);
 int tr_scene_set_stream(tr_scene* s, void* cuda_stream);                          /* run on the caller's cudaStream_t (NULL = scene's own) */
 int tr_scene_device_frame(tr_scene* s, void** device_ptr_rgb8_topdown);
-/* Test hook: bit 0 makes the occlusion samples always take the range-tested division (k_shade.cuh occlusion_gray picks
- * between two forms of the same arithmetic per pixel; results must not depend on the choice). */
+/* Test hooks: bit 0 makes the occlusion samples always take the range-tested division (k_shade.cuh occlusion_gray picks
+ * between two forms of the same arithmetic per pixel; results must not depend on the choice); bit 1 makes single-frame
+ * renders launch the tile kernel in its batch CTA shape (128 threads), so that shape can be timed on a lone frame. */
 int tr_scene_set_debug_flags(tr_scene* s, uint32_t flags);           /* zero-copy access for tests / interop */
 int tr_scene_timer_begin(tr_scene* s);                                            /* CUDA event on the scene stream */
 int tr_scene_timer_end(tr_scene* s, float* elapsed_ms);                           /* records + synchronises */
@@ -166,8 +169,20 @@ int tr_selftest_sqrt(int device, uint64_t* mismatches, uint64_t* accepted);
  * addresses, warp = 8x4 pixel block, `rounds` updating atomics per key; *atomics_per_second is the best of `repeats`
  * timed launches (CUDA events).  Not on the render path: k_raster resolves visibility in registers. */
 int tr_bench_atomic_min(int device, uint32_t width, uint32_t height, uint32_t rounds, uint32_t repeats, double* atomics_per_second);
-void* tr_host_alloc(size_t bytes);                                                /* pinned host memory for fast get_* copies */
+/* Host frames.  tr_host_alloc returns pinned, device-mapped, ZEROED host memory.  Frames delivered into it
+ * (tr_scene_render_views' `frames`, tr_scene_get_frame_buffer's dst — the clone of scene.rs:92-97) travel SPARSELY
+ * (k_host.cuh): the device stores, straight over PCIe into the destination frame, only the 64-pixel tile rows that hold
+ * a non-zero byte now and zeros into those that held one after the previous delivery to the same address; a 4K diablo
+ * frame is ~5 MB instead of 24.9 MB on the link.  The caller always finds the exact top-down RGB8 frame.  Contract: between
+ * deliveries nobody but the library writes to the memory; after writing to it yourself call tr_host_invalidate on the
+ * range (the next delivery then rewrites whole frames).  Any other destination pointer (malloc, numpy, foreign pinned
+ * memory) takes a plain full-frame copy.  TINYR_NO_SPARSE_D2H=1 in the environment forces the full copy everywhere. */
+void* tr_host_alloc(size_t bytes);
 void tr_host_free(void* p);
+int tr_host_invalidate(void* p, size_t bytes);
+/* out[0] bytes stored into host frames by the sparse delivery, out[1] tile rows stored, out[2] frames delivered sparsely,
+ * out[3] frames delivered by a full copy, out[4] bytes of those copies; reset != 0 zeroes the counters. */
+int tr_scene_transfer_stats(tr_scene* s, uint64_t out[5], int reset);
 
 /* ---- asset loaders kept from the reference (app.rs:87-131) ------------------------------------------- */
 typedef struct tr_mesh {

@@ -339,3 +339,81 @@ def test_ao_batch_with_unfiltered_lights(tinyr, oracle):
         o2.set_camera(c[0:3], c[3:6], c[6:9])
         assert np.array_equal(total, o2.render_ao(lights))
         g.close()
+
+
+def test_sparse_host_frames_are_exact_over_changing_views(tinyr):
+    """K10 (k_host.cuh): frames delivered into tr_host_alloc memory cross PCIe sparsely (non-zero tile rows + rows that
+    turned black since the last delivery to the same address).  The same pinned destination receives batches of
+    DIFFERENT views, silhouettes growing, shrinking and moving; after every delivery every frame must be
+    byte-identical to the single-frame render copied the plain way, and fewer bytes than whole frames travel."""
+    from tiny_renderer_b200.scene import Scene
+    m = get_model("diablo")
+    w, h = 1280, 720                       # pitch 3840 B: 16-byte rows, partial tile row at the top (720 = 22.5 x 32)
+    n = 5
+    g = Scene(w, h, m, "phong", ring=3)
+    single = Scene(w, h, m, "phong")
+    pinned = tinyr.pinned_empty((n, h, w, 3), np.uint8)
+    assert not pinned.any()                # tr_host_alloc memory is zeroed
+    g.transfer_stats(reset=True)
+    for batch in range(4):
+        views = turntable(n, light_angle=0.7 + batch, phase=0.37 * batch)
+        if batch == 2:                     # a close-up and a far view: the covered area changes a lot between deliveries
+            views[:, 0:3] *= np.linspace(0.5, 2.5, n, dtype=np.float32)[:, None]
+        g.render_views(views, want_checksums=False, frames_out=pinned)
+        for k in range(n):
+            parity.drive(single, views[k, 0:3], views[k, 3:6], views[k, 6:9], views[k, 9:12])
+            plain = np.empty((h, w, 3), np.uint8)           # ordinary memory: the full-copy path
+            single.get_frame_buffer(out=plain)
+            assert np.array_equal(pinned[k], plain), (batch, k)
+    st = g.transfer_stats()
+    assert st["frames_sparse"] == 4 * n and st["frames_copied"] == 0
+    assert 0 < st["sparse_bytes"] < 0.6 * 4 * n * w * h * 3, st
+    # the caller scribbles over a frame and says so: the next delivery repairs all of it
+    pinned[1] = 77
+    tinyr.host_invalidate(pinned[1])
+    views = turntable(n, phase=1.0)
+    g.render_views(views, want_checksums=False, frames_out=pinned)
+    for k in range(n):
+        parity.drive(single, views[k, 0:3], views[k, 3:6], views[k, 6:9], views[k, 9:12])
+        assert np.array_equal(pinned[k], single.get_frame_buffer()), k
+    # get_frame_buffer into pinned memory takes the same path (incl. an uncleared, twice-rendered frame and a cleared one)
+    one = tinyr.pinned_empty((h, w, 3), np.uint8)
+    for clear in (True, False, True):
+        v = views[2 if clear else 3]
+        parity.drive(single, v[0:3], v[3:6], v[6:9], v[9:12], clear=clear)
+        single.get_frame_buffer(out=one)
+        assert np.array_equal(one, single.get_frame_buffer())
+    single.clear()
+    single.get_frame_buffer(out=one)
+    assert not one.any()
+    # odd pitch (not a multiple of 16 bytes): falls back to the plain copy, still exact
+    odd = Scene(333, 201, m, "phong")
+    po = tinyr.pinned_empty((201, 333, 3), np.uint8)
+    parity.drive(odd, views[0, 0:3], views[0, 3:6], views[0, 6:9], views[0, 9:12])
+    odd.get_frame_buffer(out=po)
+    assert np.array_equal(po, odd.get_frame_buffer())
+    assert odd.transfer_stats()["frames_sparse"] == 0
+    g.close(); single.close(); odd.close()
+
+
+def test_sparse_host_frames_geometry_change_and_4k(tinyr):
+    """The same pinned block reused with another frame geometry (records of the old frames are void), and a 4K frame
+    (half-height tile row at the top, 60 whole tile columns)."""
+    from tiny_renderer_b200.scene import Scene
+    m = get_model("diablo")
+    block = tinyr.pinned_empty((3840 * 2160 * 3,), np.uint8)
+    a = Scene(1920, 1080, m, "darboux")
+    v = turntable(3)
+    parity.drive(a, v[0, 0:3], v[0, 3:6], v[0, 6:9], v[0, 9:12])
+    fa = block[:1920 * 1080 * 3].reshape(1080, 1920, 3)
+    a.get_frame_buffer(out=fa)
+    assert np.array_equal(fa, a.get_frame_buffer())
+    b = Scene(3840, 2160, m, "darboux")
+    fb = block.reshape(2160, 3840, 3)
+    for k in (1, 2):
+        parity.drive(b, v[k, 0:3], v[k, 3:6], v[k, 6:9], v[k, 9:12])
+        b.get_frame_buffer(out=fb)
+        assert np.array_equal(fb, b.get_frame_buffer()), k
+    st = b.transfer_stats()
+    assert st["frames_sparse"] == 2 and st["sparse_bytes"] < 1.5 * 3840 * 2160 * 3     # first one whole, second sparse
+    a.close(); b.close()

@@ -109,6 +109,7 @@ def lib():
             "tr_selftest_round_u32": [ctypes.c_int, ctypes.POINTER(ctypes.c_uint64)],
             "tr_bench_atomic_min": [ctypes.c_int, u32, u32, u32, u32, ctypes.POINTER(ctypes.c_double)],
             "tr_selftest_exact_quotient": [ctypes.c_int, ctypes.c_uint64, ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)],
+            "tr_host_invalidate": [vp, ctypes.c_size_t], "tr_scene_transfer_stats": [vp, vp, i32],
             "tr_ao_generate_lights": [vp, u32, vp, vp, ctypes.c_uint64, u32, ctypes.c_float, vp, ctypes.POINTER(ctypes.c_uint64)],
         }
         for name, argtypes in sig.items():
@@ -137,4 +138,4 @@ def _f3(v):
 
 
 from .scene import (Scene, Model, load_obj, load_tga, write_tga, load_model_dir, checksum_rgb8, device_count, pinned_empty,  # noqa: E402,F401
-                    generate_ao_lights, AO_LIGHT_SEED, AO_NDC_MARGIN, bench_atomic_min)
+                    generate_ao_lights, AO_LIGHT_SEED, AO_NDC_MARGIN, bench_atomic_min, host_invalidate)

@@ -10,6 +10,7 @@
 #include "k_shade.cuh"
 #include "k_misc.cuh"
 #include "k_peer.cuh"
+#include "k_host.cuh"
 
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -17,6 +18,8 @@
 #include <cstring>
 #include <string>
 #include <algorithm>
+#include <map>
+#include <mutex>
 #include <vector>
 
 using namespace tr;
@@ -78,8 +81,10 @@ struct tr_scene {
     uint32_t peer_world = 0, peer_rank = 0, peer_value = 1;
     int* peer_status = nullptr;        // mapped host word the kernel sets when a barrier times out
     AoList ao_list{};                  // covered pixels of the camera view (many-light AO batch), allocated on first use
-    uint32_t ao_list_n = 0;
     unsigned long long* diag = nullptr;
+    // K10 (k_host.cuh): [0] bytes / [1] tile rows stored into host frames by the sparse delivery; host-side counters beside them
+    unsigned long long* host_stats = nullptr;
+    uint64_t frames_sparse = 0, frames_copied = 0, bytes_copied = 0;
     unsigned long long* d_checksums = nullptr; size_t checksum_cap = 0;
     uint8_t* scratch = nullptr; size_t scratch_bytes = 0;
     cudaArray_t arrays[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -338,6 +343,8 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
     CU(cudaMemset(s->ao, 0, ao_alloc_words(s->n_px) * 4));
     CU(cudaMalloc(&s->diag, D_COUNT * 8));
     CU(cudaMemset(s->diag, 0, D_COUNT * 8));
+    CU(cudaMalloc(&s->host_stats, 16));
+    CU(cudaMemset(s->host_stats, 0, 16));
     const tr_image* imgs[4] = {&d->texture, &d->normal_map, &d->normal_map_tangent, &d->specular_map};
     for (int k = 0; k < 4; ++k) if ((rc = upload_map(s, k, *imgs[k]))) return rc;
     CU(cudaEventCreate(&s->ev_begin));
@@ -377,7 +384,7 @@ void destroy_impl(tr_scene* s) {
         cudaFree(sl.cam.rec); cudaFree(sl.cam.var); cudaFree(sl.cam.bbox); cudaFree(sl.lit.rec); cudaFree(sl.lit.bbox);
         cudaFree(sl.bins.count); cudaFree(sl.bins.list);
     }
-    cudaFree(s->geom); cudaFree(s->tile_order); cudaFree(s->ao); cudaFree(s->ao_list.frag); cudaFree(s->ao_list.pix); cudaFree(s->ao_list.count); cudaFree(s->diag); cudaFree(s->d_checksums); cudaFree(s->scratch);
+    cudaFree(s->geom); cudaFree(s->tile_order); cudaFree(s->ao); cudaFree(s->ao_list.frag); cudaFree(s->ao_list.pix); cudaFree(s->ao_list.count); cudaFree(s->diag); cudaFree(s->host_stats); cudaFree(s->d_checksums); cudaFree(s->scratch);
     if (s->own_stream) cudaStreamDestroy(s->own_stream);
     delete s;
 }
@@ -443,7 +450,8 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     dim3 grid(s->tiles_x * s->tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
     // CTA shape: 256 threads for a lone frame, 128 for overlapped batches (k_raster.cuh)
-#define TR_RASTER(M) do { if (s->overlapping) launch_raster<M, kRasterThreadsBatch>(s, grid, a, sa, u); \
+    const bool batch_shape = s->overlapping || (s->debug_flags & 2u) != 0u;      // (debug bit 1: time the batch shape on a lone frame)
+#define TR_RASTER(M) do { if (batch_shape) launch_raster<M, kRasterThreadsBatch>(s, grid, a, sa, u); \
                           else launch_raster<M, kRasterThreads>(s, grid, a, sa, u); } while (0)
     switch (mode) {
         case kModeDepthOnly: TR_RASTER(kModeDepthOnly); break;
@@ -462,7 +470,8 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
 }
 
 // K6: deferred occlusion pass of the many-light AO batch.
-// K6 part 1: compact the covered pixels of the camera slot (depth + world position), once per AO batch.
+// K6 part 1: compact the covered pixels of the camera slot (depth + world position), once per AO batch.  The count
+// stays on the device: K6 part 2 reads it there, so the batch never waits for the host.
 int run_ao_compact(tr_scene* s, const Uniforms& u) {
     if (!s->ao_list.frag) {
         CU(cudaMalloc(&s->ao_list.frag, s->n_px * sizeof(float4)));
@@ -476,20 +485,17 @@ int run_ao_compact(tr_scene* s, const Uniforms& u) {
         Scoped sp(s, KS_AO);
         k_ao_compact<<<grid, kShadeThreads, 0, s->stream>>>(a, u, s->ao_list);
     }
-    int rc = launch_ok("k_ao_compact");
-    if (rc) return rc;
-    CU(cudaMemcpyAsync(&s->ao_list_n, s->ao_list.count, 4, cudaMemcpyDeviceToHost, s->stream));
-    CU(cudaStreamSynchronize(s->stream));       // the per-light grids are sized by the count
-    return TR_OK;
+    return launch_ok("k_ao_compact");
 }
 
-// K6 part 2: one light's occlusion term for every covered pixel, added into the accumulator.
+// K6 part 2: one light's occlusion term for every covered pixel, added into the accumulator.  A fixed grid walks the
+// compacted list (grid-stride), whose length it reads from device memory.
 int run_ao_accumulate(tr_scene* s, const Uniforms& u) {
-    if (s->ao_list_n == 0) return TR_OK;
     ShadeArgs a = shade_args(s, false);                  // shadow buffer of the current (light) slot
-    dim3 grid((s->ao_list_n + kShadeThreads - 1) / kShadeThreads);
+    const size_t want = (s->n_px + kShadeThreads - 1) / kShadeThreads;
+    dim3 grid((unsigned)std::min<size_t>(want, (size_t)kAoGridCtas));
     Scoped sp(s, KS_AO);
-    k_ao_accumulate<<<grid, kShadeThreads, 0, s->stream>>>(a, u, s->ao_list, s->ao_list_n);
+    k_ao_accumulate<<<grid, kShadeThreads, 0, s->stream>>>(a, u, s->ao_list);
     return launch_ok("k_ao_accumulate");
 }
 
@@ -526,6 +532,8 @@ int checksum_into(tr_scene* s, const uint8_t* img, size_t n_bytes, unsigned long
     k_checksum<<<148 * 4, 256, 0, s->stream>>>(reinterpret_cast<const uint32_t*>(img), n_bytes / 4, d_out);
     return launch_ok("k_checksum");
 }
+
+int deliver_frame(tr_scene* s, uint8_t* dst);      // tinyr_batch.inc: sparse store into tr_host_alloc memory, else a plain copy
 
 }  // namespace
 
@@ -613,7 +621,7 @@ int tr_scene_get_frame_buffer(tr_scene* s, uint8_t* dst) {
     CU(cudaSetDevice(s->device));
     int rc = materialise(s);
     if (rc) return rc;
-    CU(cudaMemcpyAsync(dst, S(s).rgb, s->n_px * 3, cudaMemcpyDeviceToHost, s->stream));
+    if ((rc = deliver_frame(s, dst))) return rc;
     CU(cudaStreamSynchronize(s->stream));
     return TR_OK;
 }

@@ -89,8 +89,15 @@ def generate_ao_lights(positions, n_lights, seed=AO_LIGHT_SEED, look_at=(0.0, 0.
     return out, int(drawn.value)
 
 
+def host_invalidate(array):
+    """Tell the library that the caller wrote into a pinned_empty() array (tr_host_invalidate): the next frames delivered
+    into it are rewritten whole instead of sparsely."""
+    _check(lib().tr_host_invalidate(array.ctypes.data, array.nbytes))
+
+
 def pinned_empty(shape, dtype):
-    """numpy array over cudaMallocHost memory (fast D2H for the get_* calls).  Freed with the array."""
+    """numpy array over tr_host_alloc memory: pinned, device-mapped, zeroed; frames delivered into it travel sparsely
+    (include/tinyr.h "Host frames").  Freed with the array."""
     dtype = np.dtype(dtype)
     n = int(np.prod(shape)) * dtype.itemsize
     p = lib().tr_host_alloc(max(n, 1))
@@ -155,7 +162,8 @@ class Scene:
     __del__ = close
 
     def set_debug_flags(self, flags):
-        """Test hook (tr_scene_set_debug_flags): bit 0 = occlusion samples always use the range-tested division."""
+        """Test hooks (tr_scene_set_debug_flags): bit 0 = occlusion samples always use the range-tested division, bit 1 =
+        single-frame renders use the batch CTA shape of the tile kernel."""
         _check(lib().tr_scene_set_debug_flags(self._h, int(flags)))
 
     # ---- reference surface ----
@@ -263,6 +271,13 @@ class Scene:
 
     def ao_close_peers(self):
         _check(lib().tr_scene_ao_close_peers(self._h))
+
+    def transfer_stats(self, reset=False):
+        """Host-frame delivery counters (tr_scene_transfer_stats)."""
+        o = np.zeros(5, np.uint64)
+        _check(lib().tr_scene_transfer_stats(self._h, o.ctypes.data, 1 if reset else 0))
+        return {"sparse_bytes": int(o[0]), "sparse_rows": int(o[1]), "frames_sparse": int(o[2]), "frames_copied": int(o[3]),
+                "copied_bytes": int(o[4])}
 
     def set_stream(self, cuda_stream):
         _check(lib().tr_scene_set_stream(self._h, ctypes.c_void_p(cuda_stream)))
