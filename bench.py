@@ -5,18 +5,21 @@
     python bench.py --impl reference --gpus 1 --steps K ...  # the reference's CPU path (oracle port) on host cores
     torchrun ... bench.py --gpus N ...                       # one rank per GPU, weak scaling over view batches
 
-Metric (BASELINE.json): Mpixels/s shaded, device-timed, at 3840x2160.  Workload at every N = BASELINE config 2:
-diablo, phong + darboux, 3840x2160, 8 camera angles 2*pi*k/8, light angle 0.7 rad -> one step = 16 frames per
-GPU, each `clear; set_light_direction; set_camera; render` (app.rs:170,208-210).  N > 1 shards independent view
-batches (no data-path collective) and additionally reports the many-light AO mode (config 4: lights sharded,
-one NCCL all-reduce of the u32 accumulators) under "ao".
+Metric (BASELINE.json): Mpixels/s shaded, device-timed, at 3840x2160.  Workload at every N = BASELINE config 2 as a
+turntable: diablo, phong + darboux, 3840x2160, 64 camera angles 2*pi*k/64, light angle 0.7 rad; one step = REPS
+turns of both pipelines = 2 * 64 * REPS frames per GPU, each `clear; set_light_direction; set_camera; render`
+(app.rs:170,208-210).  With 64 angles on 8 frame slots every slot renders a different view each time it comes round,
+so tile-state flips, zero-fills and the read-back's damage tracking all run inside the timed region (r1 used 8 angles
+on 8 slots: every slot re-rendered the same frame; that figure is reported once as `aliased_8_angles`).  N > 1 shards
+independent view batches (no data-path collective).  Beside the headline the line carries BASELINE's other configs:
+`shadow4k` (config 3), `ao` (config 4: 1024 lights sharded, one sum of the u32 accumulators) and `views8k` (config 5:
+4096-view specular turntable at 7680x4320, views sharded, strong scaling).
 """
 import argparse
 import json
 import math
 import os
 import statistics
-import subprocess
 import sys
 import threading
 import time
@@ -28,12 +31,19 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 W4K, H4K = 3840, 2160
+W8K, H8K = 7680, 4320
 METRIC = "Mpixels/s shaded (device-timed) at 3840x2160"
 PIPES = ("phong", "darboux")
-N_ANGLES = 8
+PIPE_ID = {"default": 0, "phong": 1, "normal_map": 2, "specular": 3, "darboux": 4, "shadow": 5, "occlusion": 6}
+N_ANGLES = 64
 LIGHT_ANGLE = 0.7
-PREROLL_STEPS = 2   # untimed steps queued directly in front of the timed ones (see run_gpu)
+QUICK = os.environ.get("TINYR_BENCH_QUICK") == "1"          # smoke-test sizes (never a bench value)
+REPS = int(os.environ.get("TINYR_BENCH_REPS", "1" if QUICK else "8"))   # turns of the 64-angle turntable per step
+PREROLL_STEPS = 1   # untimed steps queued directly in front of the timed ones (see timed_batches)
 RING = int(os.environ.get("TINYR_RING", "8"))   # frame slots per scene: 8 x (8 B keys + 3 B rgb) x 8.29 Mpx = 730 MB of render targets > 126 MB L2
+E2E_HOST_FRAMES = 16    # pinned host frames per scene that the e2e leg delivers into, round robin
+VIEWS_8K = 64 if QUICK else 4096
+AO_LIGHTS = 32 if QUICK else 1024
 
 
 def load_peaks():
@@ -44,27 +54,36 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def bench_model():
+def bench_model(name="diablo"):
     import assets
-    m = assets.get_model("diablo")
-    data = "reference asset diablo (staged copy of /root/reference/assets), synthetic views" if m.name == "diablo" \
+    m = assets.get_model(name)
+    data = ("reference asset %s (staged copy of /root/reference/assets), synthetic views" % name) if m.name == name \
         else "synthetic procedural model (reference assets not staged), synthetic views"
     return m, data
 
 
-def view_batch(rank=0):
-    """8 camera angles (rank offsets the phase so ranks do not render identical frames), app.rs:200-207."""
+def view_batch(n_angles=N_ANGLES, rank=0, light_angle=LIGHT_ANGLE):
+    """Turntable camera angles 2*pi*k/n (rank offsets the phase so ranks do not render identical frames), app.rs:200-207."""
     import assets
-    v = np.zeros((N_ANGLES, 12), np.float32)
-    for k in range(N_ANGLES):
-        lf, la, up, light = assets.view_vectors(2 * math.pi * k / N_ANGLES + 0.01 * rank, LIGHT_ANGLE)
+    v = np.zeros((n_angles, 12), np.float32)
+    for k in range(n_angles):
+        lf, la, up, light = assets.view_vectors(2 * math.pi * k / n_angles + 0.01 * rank, light_angle)
         v[k, 0:3], v[k, 3:6], v[k, 6:9], v[k, 9:12] = lf, la, up, light
     return v
 
 
+def views_8k(lo, hi, n_per_model):
+    """Config 5: view j of a model uses camera angle 2*pi*j/n_per_model, light angle 0.7 rad."""
+    import assets
+    v = np.zeros((hi - lo, 12), np.float32)
+    for i, j in enumerate(range(lo, hi)):
+        lf, la, up, light = assets.view_vectors(2 * math.pi * j / n_per_model, LIGHT_ANGLE)
+        v[i, 0:3], v[i, 3:6], v[i, 6:9], v[i, 9:12] = lf, la, up, light
+    return v
+
+
 class ClockSampler:
-    """SM clock and throttle reasons DURING the timed region, sampled through NVML from a thread every ~2 ms
-    (the timed region of a default run is well under a second, too short for `nvidia-smi -lms`)."""
+    """SM clock, power and throttle reasons DURING the timed region, sampled through NVML from a thread every ~2 ms."""
     REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
 
     def __init__(self, index):
@@ -83,7 +102,8 @@ class ClockSampler:
             while not self.stop_flag:
                 try:
                     self.rows.append((pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM),
-                                      pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)))
+                                      pynvml.nvmlDeviceGetCurrentClocksEventReasons(h),
+                                      pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0))
                 except Exception:
                     pass
                 time.sleep(0.002)
@@ -100,86 +120,135 @@ class ClockSampler:
         for r in self.rows:
             mask |= int(r[1])
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.max_mhz,
-                "reasons": [n for n, bit in self.REASONS if mask & bit], "samples": len(sm)}
+                "reasons": [n for n, bit in self.REASONS if mask & bit], "samples": len(sm),
+                "power_w_max": max((r[2] for r in self.rows), default=None)}
 
 
 # ---- CPU side: the reference's own CPU path, as restated by the oracle (Rust cannot be compiled here) --------
 
-def cpu_render_frames(model, jobs, threads):
-    """jobs: list of (pipeline, view_row).  Each worker owns its OracleScenes (ctypes releases the GIL)."""
-    import oracle_lib
-    lock, pos = threading.Lock(), [0]
+class CpuPool:
+    """Persistent host worker threads, each owning its OracleScenes (built BEFORE any timed region; ctypes releases the
+    GIL during a render).  run(jobs) renders every job — (scene key, view row) — and returns the wall time."""
 
-    def worker():
-        scenes = {}
-        while True:
-            with lock:
-                i = pos[0]
-                pos[0] += 1
-            if i >= len(jobs):
-                return
-            pipe, v = jobs[i]
-            s = scenes.get(pipe)
-            if s is None:
-                s = scenes[pipe] = oracle_lib.OracleScene(W4K, H4K, model, pipe)
-            s.clear(); s.set_light_direction(v[9:12]); s.set_camera(v[0:3], v[3:6], v[6:9]); s.render()
-            s.get_frame_buffer()
+    def __init__(self, model_of, scene_keys, threads):
+        import oracle_lib
+        self.threads = threads
+        self.jobs, self.pos, self.lock = [], [0], threading.Lock()
+        self.start, self.done = threading.Barrier(threads + 1), threading.Barrier(threads + 1)
+        self.quit = False
+        ready = threading.Barrier(threads + 1)
 
-    # scene construction (buffer allocation) happens inside the timed region for the first job of each worker;
-    # it is ~10 ms against >= 300 ms per 4K frame.
-    t0 = time.perf_counter()
-    ts = [threading.Thread(target=worker) for _ in range(threads)]
-    [t.start() for t in ts]
-    [t.join() for t in ts]
-    return time.perf_counter() - t0
+        def worker():
+            scenes = {key: oracle_lib.OracleScene(key[2], key[3], model_of[key[0]], key[1]) for key in scene_keys}
+            for s in scenes.values():       # touch every page of the buffers once
+                s.clear()
+            ready.wait()
+            while True:
+                self.start.wait()
+                if self.quit:
+                    return
+                while True:
+                    with self.lock:
+                        i = self.pos[0]
+                        self.pos[0] += 1
+                    if i >= len(self.jobs):
+                        break
+                    key, v = self.jobs[i]
+                    s = scenes[key]
+                    s.clear(); s.set_light_direction(v[9:12]); s.set_camera(v[0:3], v[3:6], v[6:9]); s.render()
+                    s.get_frame_buffer()
+                self.done.wait()
+
+        self.workers = [threading.Thread(target=worker, daemon=True) for _ in range(threads)]
+        [t.start() for t in self.workers]
+        ready.wait()
+
+    def run(self, jobs):
+        self.jobs, self.pos[0] = jobs, 0
+        t0 = time.perf_counter()
+        self.start.wait()
+        self.done.wait()
+        return time.perf_counter() - t0
+
+    def close(self):
+        self.quit = True
+        self.start.wait()
+        [t.join() for t in self.workers]
 
 
-def cpu_baseline(model, n_frames_per_pipe=2):
-    """Faithful single-thread baseline (the reference's render loop is single-threaded, scene.rs:151) on a
-    bounded sample of the same workload: n views of each pipeline at 3840x2160."""
-    views = view_batch()
-    jobs = [(p, views[k]) for p in PIPES for k in range(n_frames_per_pipe)]
-    secs = cpu_render_frames(model, jobs, 1)
-    return {"value": len(jobs) * W4K * H4K / secs / 1e6, "unit": "Mpixels/s", "cores": 1, "kind": "port",
-            "sample": "%d frames (%d views x phong+darboux) at 3840x2160, oracle C++ port of scene.rs/shader.rs, 1 thread, %.2f s"
-                      % (len(jobs), n_frames_per_pipe, secs)}
+def ao_lights_host(model, n):
+    """The seeded light list of config 4 WITHOUT the product library: the committed fixture for diablo, else the Python
+    twin of tr_ao_generate_lights (tests/ao_lights_py.py)."""
+    fixture = os.path.join(ROOT, "tests", "golden", "ao_lights_diablo_1024.npy")
+    if model.name == "diablo" and os.path.exists(fixture):
+        return np.load(fixture)[:n]
+    import ao_lights_py
+    return ao_lights_py.generate(model.positions, n)[0]
 
 
-def cpu_ao_baseline(model, n_lights, threads):
-    """BASELINE config 4 on the host: per light the reference's sequence set_light_direction / clear / render with the
-    occlusion pipeline (both passes, shader.rs:806-963) at 3840x2160, camera angle 0 — what tr_scene_render_ao sums.  A
-    bounded sample of the 1,024 lights (the first n of the same seeded list), one light per host thread."""
+def ao_jobs(model, n_lights, key):
     import assets
-    import tiny_renderer_b200 as tr
-    lights, _ = tr.generate_ao_lights(model.positions, n_lights)
     lf, la, up, _ = assets.view_vectors(0.0, 0.0)
     jobs = []
-    for l in lights:
+    for l in ao_lights_host(model, n_lights):
         v = np.zeros(12, np.float32)
         v[0:3], v[3:6], v[6:9], v[9:12] = lf, la, up, l
-        jobs.append(("occlusion", v))
-    secs = cpu_render_frames(model, jobs, threads)
-    return {"value": n_lights / secs, "unit": "passes/s", "cores": threads, "kind": "port",
-            "sample": "%d of the %d light directions at 3840x2160, oracle C++ port of the occlusion pipeline, %d thread%s, %.2f s"
-                      % (n_lights, AO_LIGHTS, threads, "" if threads == 1 else "s", secs)}
+        jobs.append((key, v))
+    return jobs
+
+
+def cpu_baselines(model, head):
+    """Faithful single-thread baselines (the reference's render loop is single-threaded, scene.rs:151; its ThreadPool is
+    never used, scene.rs:72-74) on bounded samples of the same workloads, scenes built before the timed region."""
+    views = view_batch()
+    k4 = [("diablo", p, W4K, H4K) for p in PIPES] + [("diablo", "shadow", W4K, H4K), ("diablo", "occlusion", W4K, H4K)]
+    k8 = [("head", "specular", W8K, H8K), ("diablo", "specular", W8K, H8K)]
+    pool = CpuPool({"diablo": model, "head": head}, k4 + k8, 1)
+    out = {}
+    jobs = [(k4[i], views[8 * k]) for i in range(2) for k in range(2)]
+    secs = pool.run(jobs)
+    out["main"] = {"value": len(jobs) * W4K * H4K / secs / 1e6, "unit": "Mpixels/s", "cores": 1, "kind": "port",
+                   "sample": "%d frames (2 views x phong+darboux) at 3840x2160, oracle C++ port of scene.rs/shader.rs, 1 thread, %.2f s"
+                             % (len(jobs), secs)}
+    jobs = [(k4[2], view_batch(light_angle=2.1)[8]), (k4[2], views[24])]
+    secs = pool.run(jobs)
+    out["shadow4k"] = {"value": len(jobs) * W4K * H4K / secs / 1e6, "unit": "Mpixels/s", "cores": 1, "kind": "port",
+                       "sample": "%d shadow frames at 3840x2160 (both passes), oracle port, 1 thread, %.2f s" % (len(jobs), secs)}
+    n = 3
+    secs = pool.run(ao_jobs(model, n, k4[3]))
+    out["ao"] = {"value": n / secs, "unit": "passes/s", "cores": 1, "kind": "port",
+                 "sample": "%d of the %d light directions at 3840x2160, oracle C++ port of the occlusion pipeline "
+                           "(set_light_direction / clear / render per light, shader.rs:806-963), 1 thread, %.2f s" % (n, AO_LIGHTS, secs)}
+    v8 = views_8k(0, 2048, 2048)
+    jobs = [(k8[0], v8[0]), (k8[0], v8[700]), (k8[1], v8[0]), (k8[1], v8[700])]
+    secs = pool.run(jobs)
+    out["views8k"] = {"value": len(jobs) * W8K * H8K / secs / 1e6, "unit": "Mpixels/s", "cores": 1, "kind": "port",
+                      "sample": "4 of the 4096 views (2 african_head + 2 diablo, specular) at 7680x4320, oracle port, 1 thread, %.2f s" % secs}
+    pool.close()
+    return out
 
 
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU implementation of the path (the oracle port — the Rust crate cannot
-    be built on this box) on all host threads it can use, same config/metric/unit."""
+    be built on this box) on all host threads it can use, same config/metric/unit.  Worker threads and their scenes
+    are created before the timed loop; nothing of the product library is loaded."""
     if rank != 0:
         return
     model, data = bench_model()
     cores = os.cpu_count() or 1
     views = view_batch()
-    # One reference step = a bounded sample of the GPU arm's step (16 frames): 2..8 of the 8 views of each pipeline, so
-    # that any --steps K the driver passes ends within minutes (a 4K frame costs ~0.15-0.5 s of one host core).
-    sample_views = max(2, min(N_ANGLES, cores // len(PIPES)))      # enough frames to occupy every host thread
-    jobs = [(p, views[k]) for p in PIPES for k in range(sample_views)]
+    # One reference step = a bounded sample of the GPU arm's step: one frame per host thread, spread evenly over the 64
+    # angles and alternating between the two pipelines, so that any --steps K ends within minutes (a 4K frame costs
+    # ~0.15-0.5 s of one host core).
+    n_jobs = max(4, cores)
+    keys = [("diablo", p, W4K, H4K) for p in PIPES]
+    jobs = [(keys[i % 2], views[((i // 2) * N_ANGLES // max(1, n_jobs // 2)) % N_ANGLES]) for i in range(n_jobs)]
     threads = min(cores, len(jobs))
+    occ = ("diablo", "occlusion", W4K, H4K)
+    pool = CpuPool({"diablo": model}, keys + [occ], threads)
     times = []
     for i in range(args.warmup + args.steps):
-        t = cpu_render_frames(model, jobs, threads)
+        t = pool.run(jobs)
         if i >= args.warmup:
             times.append(t)
     total = sum(times)
@@ -189,19 +258,26 @@ def run_reference(args, rank, world):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": data,
             "config": workload_config(),
             "cpu_baseline": {"value": value, "unit": "Mpixels/s", "cores": threads, "kind": "port",
-                             "sample": "%d frames per step (%d views x phong+darboux) at 3840x2160, oracle C++ port of "
-                                       "scene.rs/shader.rs, one frame per host thread, %d threads" % (len(jobs), sample_views, threads)},
+                             "sample": "%d frames per step (phong + darboux alternating, angles spread over the turntable) at "
+                                       "3840x2160, oracle C++ port of scene.rs/shader.rs, one frame per host thread, %d persistent "
+                                       "threads, scenes built before the timed loop" % (len(jobs), threads)},
             "e2e": {"value": value, "unit": "Mpixels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     # the second half of BASELINE's metric, once per run (not per step): one light per host thread
-    ao = cpu_ao_baseline(model, threads, threads)
+    secs = pool.run(ao_jobs(model, threads, occ))
+    pool.close()
+    ao = {"value": threads / secs, "unit": "passes/s", "cores": threads, "kind": "port",
+          "sample": "%d of the %d light directions at 3840x2160, oracle port of the occlusion pipeline, one light per host thread, %.2f s"
+                    % (threads, AO_LIGHTS, secs)}
     line["ao"] = {"metric": "AO depth passes/s", "value": ao["value"], "unit": "passes/s", "cpu_baseline": ao}
     print(json.dumps(line), flush=True)
 
 
 def workload_config():
-    return {"workload": "BASELINE config 2: diablo, phong + darboux, 3840x2160, 8 camera angles 2*pi*k/8, light 0.7 rad "
-                        "(16 frames per step per GPU)", "width": W4K, "height": H4K, "frames_per_step_per_gpu": len(PIPES) * N_ANGLES,
-            "triangles": 5022, "l2": "render targets rotate through a ring of %d buffer sets per scene (%d MB of keys + RGB > 126 MB L2)" % (RING, RING * W4K * H4K * 11 // 1000000),
+    return {"workload": "BASELINE config 2 as a turntable: diablo, phong + darboux, 3840x2160, %d camera angles 2*pi*k/%d, light 0.7 rad, "
+                        "%d turns per step (%d frames per step per GPU)" % (N_ANGLES, N_ANGLES, REPS, len(PIPES) * N_ANGLES * REPS),
+            "width": W4K, "height": H4K, "frames_per_step_per_gpu": len(PIPES) * N_ANGLES * REPS,
+            "triangles": 5022, "l2": "render targets rotate through a ring of %d buffer sets per scene (%d MB of keys + RGB > 126 MB L2); "
+                                     "view k lands on slot k mod %d, so a slot never renders the same view twice in a row" % (RING, RING * W4K * H4K * 11 // 1000000, RING),
             "parallelism": "independent view batches per GPU, no data-path collective; on a GPU the phong scene and the "
                            "darboux scene run on a stream each, frames of a scene overlap on its %d frame slots" % RING,
             "preroll_steps": PREROLL_STEPS}
@@ -209,51 +285,52 @@ def workload_config():
 
 # ---- GPU arm -----------------------------------------------------------------------------------------------
 
+N_MAPS = {"default": 1, "phong": 1, "shadow": 1, "normal_map": 2, "darboux": 2, "specular": 3, "occlusion": 0}
+
+
 def algorithmic_bytes(n_px, covered, n_tri, pipe):
-    """SURVEY.md §8(d) / BASELINE.md §3: B_frame = 19*P + n_maps*min(3*C, 3 MiB) + geometry, split per kernel.
+    """SURVEY.md §8(d) / BASELINE.md §3: B_frame = 19*P + n_maps*min(3*C, 3 MiB) + geometry (+ 8*P for the shadow
+    pipeline's light-depth buffer: one write, one read), split per kernel.
     K1 vertex_setup: static geometry (96 B) read, setup record (64 B) + bbox (16 B) + varyings written per polygon.
-    K3+K5 (one fused tile kernel since r1b): the visibility + shading part of the formula, 19*P (key write 8*P,
-    key read 8*P, RGB write 3*P — the fused kernel keeps the key read on chip and skips the keys of empty
-    tiles, so its DRAM traffic is BELOW this figure; the algorithmic figure is kept as the common yardstick)
-    + compulsory texels + setup records/varyings of the polygons read once."""
-    n_maps = {"phong": 1, "darboux": 2}[pipe]
-    tex = n_maps * min(3 * covered, 3 << 20)
+    K3+K5 (one fused tile kernel): the visibility + shading part of the formula, 19*P (key write 8*P, key read 8*P,
+    RGB write 3*P — the fused kernel keeps the key read on chip and skips the keys of empty tiles, so its DRAM
+    traffic is BELOW this figure; the algorithmic figure is kept as the common yardstick) + compulsory texels + setup
+    records/varyings of the polygons read once."""
+    tex = N_MAPS[pipe] * min(3 * covered, 3 << 20)
     k1 = n_tri * (96 + 64 + 16 + (96 if pipe == "darboux" else 16))
     k35 = 19 * n_px + tex + n_tri * (64 + 16 + 96)
-    return {"K1_vertex_setup": k1, "K3_raster_visibility": k35, "frame": 19 * n_px + tex + k1}
+    extra = 8 * n_px + n_tri * (96 + 64 + 16) if pipe == "shadow" else 0
+    return {"K1_vertex_setup": k1, "K3_raster_visibility": k35, "frame": 19 * n_px + tex + k1 + extra}
 
 
-def ncu_kernel_summary(want):
-    """Entry of the kernel whose name contains `want` in the committed newest `ncu --set full` summary
-    (profiles/r*_traffic.json, written by tools/ncu_summary.py: DRAM bytes, duration and warp instructions per launch);
-    None when absent."""
+def ncu_summaries():
+    """The committed newest `ncu` summary (profiles/r*_traffic.json, written by tools/ncu_summary.py)."""
     import glob
     found = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))
     if not found:
-        return None
+        return {}, None
+    with open(found[-1]) as f:
+        return json.load(f), os.path.basename(found[-1])
+
+
+def ncu_kernel_summary(want):
+    """Entry of the kernel whose name contains `want` (DRAM bytes, duration and warp instructions per launch)."""
     # "k_raster<4,128>" matches ncu's spellings "k_raster<4, 128>" and "k_raster<(int)4, (int)128>"
     def norm(name):
         return name.replace("(int)", "").replace(" ", "")
-    with open(found[-1]) as f:
-        for k, v in json.load(f).items():
-            if want.replace(" ", "") in norm(k):
-                return dict(v, source=os.path.basename(found[-1]))
+    table, src = ncu_summaries()
+    for k, v in table.items():
+        if isinstance(v, dict) and want.replace(" ", "") in norm(k):
+            return dict(v, source=src)
     return None
-
-
-def ncu_traffic(pipe):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused tile kernel (None when not captured)."""
-    e = ncu_kernel_summary("k_raster<%d,256>" % {"phong": 1, "darboux": 4}[pipe])
-    return e["dram_bytes_per_launch"] if e else None
 
 
 def issue_roofline(kernels, us, n_sm, sm_mhz):
     """The bound these kernels actually run against: one warp instruction per cycle per SM sub-partition, which for
-    FP32 work is also the FP32 pipe's rate (tools/probe/ffma2_probe.cu: scalar FMUL+FADD reaches 95 % of it, packed
-    FFMA2 is half rate).  Warp instructions per launch come from the committed ncu capture of the named kernels
-    (they do not depend on timing), `us` is measured live.  None when a kernel has no capture."""
+    FP32 work is also the FP32 pipe's rate (tools/probe/ffma2_probe.cu).  Warp instructions per launch come from the
+    committed ncu capture of the named kernels (they do not depend on timing), `us` is measured live."""
     entries = [ncu_kernel_summary(k) for k in kernels]
-    if any(e is None for e in entries) or not sm_mhz:
+    if any(e is None or "warp_instructions" not in e for e in entries) or not sm_mhz:
         return None
     instr = sum(e["warp_instructions"] for e in entries)
     peak = n_sm * 4 * sm_mhz * 1e6
@@ -263,52 +340,121 @@ def issue_roofline(kernels, us, n_sm, sm_mhz):
             "frac": ach / peak, "source": entries[0]["source"]}
 
 
-def batch_roofline(us_per_frame, n_px, covered, n_tri, peak):
-    """Average algorithmic frame bytes of the step's pipelines over the measured time per frame of the timed region."""
-    nbytes = sum(algorithmic_bytes(n_px, covered[p], n_tri, p)["frame"] for p in PIPES) / len(PIPES)
-    ach = nbytes / (us_per_frame * 1e-6) / 1e9
-    return {"algorithmic_bytes_per_frame": nbytes, "us_per_frame": us_per_frame, "achieved": ach, "frac": ach / peak}
+def lone_frame_us(scene, views, reps=2):
+    """Per-kernel device time of lone frames (profiling mode: CUDA events around every launch on the scene stream,
+    one frame at a time, no overlap between frames)."""
+    v = views[0]
+    scene.clear(); scene.set_light_direction(v[9:12]); scene.set_camera(v[0:3], v[3:6], v[6:9]); scene.render(); scene.synchronize()
+    scene.set_profiling(True)
+    scene.kernel_times()
+    for _ in range(reps):
+        for v in views:
+            scene.clear(); scene.set_light_direction(v[9:12]); scene.set_camera(v[0:3], v[3:6], v[6:9]); scene.render()
+    kt = scene.kernel_times()
+    scene.set_profiling(False)
+    return {k: (t / n * 1e3) for k, (t, n) in kt.items() if n and t > 0}
 
 
-AO_LIGHTS = 1024
+def timed_batches(torch, dist, tstream, pstreams, call, steps, preroll=1):
+    """`steps` x call() between CUDA events on tstream, the scenes' streams forked from / joined into it; a barrier and a
+    device synchronize on both sides; returns ms (this rank)."""
+    def fork():
+        for ps in pstreams:
+            ps.wait_stream(tstream)
+
+    def join():
+        for ps in pstreams:
+            tstream.wait_stream(ps)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # Untimed steps behind the barrier, joined before e0: the device has drained them when the timed steps start, but
+    # the host has long since queued the timed steps behind them (r1: without this the first timed launches are fed by
+    # a host thread that has just left the barrier).
+    fork()
+    for _ in range(preroll):
+        call()
+    join()
+    e0.record()
+    fork()
+    for _ in range(steps):
+        call()
+    join()
+    e1.record()
+    barrier()
+    return e0.elapsed_time(e1)
 
 
-def run_ao(args, rank, world, dev, model, dist, stream, sm_mhz=None):
+def max_over_ranks(torch, dist, *vals):
+    if dist is not None:
+        t = torch.tensor(list(vals), device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        vals = tuple(float(x) for x in t.tolist())
+    return vals if len(vals) > 1 else vals[0]
+
+
+def sum_over_ranks(torch, dist, val):
+    if dist is None:
+        return val
+    t = torch.tensor([val], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+def weighted_checksum(a):
+    """Position-weighted 64-bit hash of a u32 image (the tr_checksum_rgb8 scheme): sum of w_i * (2 i + 1) mod 2^64 — a
+    permutation of the values changes it, unlike a plain sum."""
+    w = np.ascontiguousarray(a, np.uint32).reshape(-1).astype(np.uint64)
+    idx = np.arange(w.size, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        return int((w * (idx * np.uint64(2) + np.uint64(1))).sum(dtype=np.uint64))
+
+
+def run_ao(args, rank, world, dev, model, dist, tstream, sm_mhz=None):
     """BASELINE config 4: diablo, occlusion pipeline, 1024 light-direction depth passes at 3840x2160, lights sharded
     over the ranks (strong scaling: the light count is fixed), ONE sum of the u32 accumulators over the ranks at the
-    end (the library's kernel over NVLink peer memory).  Device-timed (CUDA events on the launching stream), max over ranks."""
+    end.  Device-timed (CUDA events on the launching stream), max over ranks.  The exchange is timed both ways, apples to
+    apples (same buffer, from a barrier, 5 back-to-back operations, max over ranks): the library's kernel over NVLink
+    peer memory and NCCL's all-reduce; the timed batch uses whichever was faster."""
     import torch
     import tiny_renderer_b200 as tr
     from tiny_renderer_b200 import multi
     from tiny_renderer_b200.scene import Scene
+    import assets
+    stream = tstream.cuda_stream
     lights, drawn = tr.generate_ao_lights(model.positions, AO_LIGHTS)
     s = Scene(W4K, H4K, model, "occlusion", device=dev, ring=RING)
     s.set_stream(stream)
-    lf, la, up, _ = __import__("assets").view_vectors(0.0, 0.0)
+    lf, la, up, _ = assets.view_vectors(0.0, 0.0)
     s.set_camera(lf, la, up)
     lo, hi = multi.shard_range(len(lights), rank, world)
-    # The sum over the ranks is the library's own kernel over NVLink peer memory (k_peer.cuh), on the scene stream
-    # behind the light passes; the NCCL all-reduce of the same buffer is timed beside it on a copy, for comparison.
     multi.connect_ao_peers(s, rank, world)
     s.render_ao(lights[lo:min(hi, lo + 8)], reset=True, read=False)          # warm-up
     acc = multi.ao_accumulator_tensor(s)
-    nccl_ms = None
+    peer_ms = nccl_ms = None
+    use_peer = True
     if dist is not None:
-        s.ao_reduce_peers()
-        s.synchronize()
-        scratch = acc.clone()
-        for _ in range(3):
-            dist.all_reduce(scratch)
-        torch.cuda.synchronize()
-        dist.barrier()
-        n0, n1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        n0.record()
-        for _ in range(5):
-            dist.all_reduce(scratch)
-        n1.record()
-        torch.cuda.synchronize()
-        nccl_ms = n0.elapsed_time(n1) / 5
-        del scratch
+        def time_exchange(op):
+            for _ in range(2):
+                op()
+            torch.cuda.synchronize()
+            dist.barrier()
+            n0, n1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            n0.record()
+            for _ in range(5):
+                op()
+            n1.record()
+            torch.cuda.synchronize()
+            return max_over_ranks(torch, dist, n0.elapsed_time(n1) / 5)
+        peer_ms = time_exchange(s.ao_reduce_peers)
+        nccl_ms = time_exchange(lambda: dist.all_reduce(acc))
+        use_peer = peer_ms <= nccl_ms
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
@@ -317,14 +463,13 @@ def run_ao(args, rank, world, dev, model, dist, stream, sm_mhz=None):
     s.render_ao(lights[lo:hi], reset=True, read=False)
     e1.record()
     if world > 1:
-        s.ao_reduce_peers()
+        if use_peer:
+            s.ao_reduce_peers()
+        else:
+            dist.all_reduce(acc)            # on tstream, behind the light passes
     e2.record()
     torch.cuda.synchronize()
-    ms, ar_ms = e0.elapsed_time(e2), e1.elapsed_time(e2)
-    if dist is not None:
-        t = torch.tensor([ms, ar_ms, nccl_ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, ar_ms, nccl_ms = float(t[0].item()), float(t[1].item()), float(t[2].item())
+    ms, ar_ms = max_over_ranks(torch, dist, e0.elapsed_time(e2), e1.elapsed_time(e2))
     total = s.read_ao()
     covered = int((s.raw_visibility() != 0xFFFFFFFF).sum())
     diag = s.diagnostics()
@@ -336,16 +481,121 @@ def run_ao(args, rank, world, dev, model, dist, stream, sm_mhz=None):
     peak, _ = load_peaks()
     us_per_pass = ms * 1e3 / max(1, hi - lo)
     n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
-    issue = issue_roofline(["k_raster<-2,128>", "k_ao_accumulate"], us_per_pass, n_sm, sm_mhz) if rank == 0 else None
+    issue = issue_roofline(["k_raster<-2,128>", "k_ao_accumulate", "k_vertex_setup<1>"], us_per_pass, n_sm, sm_mhz) if rank == 0 else None
     return {"metric": "AO depth passes/s", "value": AO_LIGHTS / (ms * 1e-3), "unit": "passes/s", "n_gpus": world,
-            "scaling": "strong", "lights": AO_LIGHTS, "lights_per_gpu": hi - lo, "ms": ms, "exchange": "k_ao_reduce_peers (own kernel, NVLink peer memory)" if world > 1 else "none",
-            "exchange_ms": ar_ms, "nccl_allreduce_ms": nccl_ms, "exchange_bytes": 4 * n_px, "us_per_pass": us_per_pass, "checksum": int(total.astype(np.uint64).sum()),
+            "scaling": "strong", "lights": AO_LIGHTS, "lights_per_gpu": hi - lo, "ms": ms,
+            "exchange": ("none" if world == 1 else "k_ao_reduce_peers (own kernel, NVLink peer memory)" if use_peer else "NCCL all-reduce (faster than the own kernel in this run)"),
+            "exchange_ms_in_batch": ar_ms, "exchange_ms_alone": {"k_ao_reduce_peers": peer_ms, "nccl_allreduce": nccl_ms,
+                                                                 "method": "5 back-to-back operations on the accumulator from a barrier, CUDA events, max over ranks"},
+            "exchange_bytes": 4 * n_px, "us_per_pass": us_per_pass,
+            "checksum": weighted_checksum(total), "checksum_kind": "sum of accum[i] * (2 i + 1) mod 2^64 (position-weighted)",
             "shadow_index_oob": diag["shadow_index_oob"], "shadow_x_wrap": diag["shadow_x_wrap"],
             "roofline": {"bound": "hbm", "algorithmic_bytes_per_pass": per_pass_bytes,
                          "achieved": per_pass_bytes / (us_per_pass * 1e-6) / 1e9, "peak": peak,
                          "frac": per_pass_bytes / (us_per_pass * 1e-6) / 1e9 / peak, "issue": issue},
             "config": "BASELINE config 4: diablo, occlusion, %d light directions (SplitMix64 seed 0x5EED0A0, %d drawn), "
                       "3840x2160, camera angle 0" % (AO_LIGHTS, drawn)}
+
+
+def run_views8k(rank, world, dev, model, head, dist, tstream):
+    """BASELINE config 5 exactly as SURVEY.md §8(d) defines it: specular at 7680x4320, 4096-view turntable, views 0-2047
+    african_head and 2048-4095 diablo (view j of a model: camera angle 2*pi*j/2048, light 0.7 rad), per-view 64-bit
+    checksums computed on the device.  Strong scaling: every rank renders a contiguous block of each model's views
+    (balanced: the head covers 1.7x the pixels of diablo), no data-path collective; only checksums are gathered."""
+    import torch
+    from tiny_renderer_b200 import multi
+    from tiny_renderer_b200.scene import Scene
+    n_per_model = VIEWS_8K // 2
+    n_px = W8K * H8K
+    lo, hi = multi.shard_range(n_per_model, rank, world)
+    scenes = {"african_head": Scene(W8K, H8K, head, "specular", device=dev, ring=RING),
+              "diablo": Scene(W8K, H8K, model, "specular", device=dev, ring=RING)}
+    pstreams = [torch.cuda.Stream(device=dev) for _ in scenes]
+    for s, ps in zip(scenes.values(), pstreams):
+        s.set_stream(ps.cuda_stream)
+    v = views_8k(lo, hi, n_per_model)
+    for s in scenes.values():
+        s.render_views(v[:min(len(v), 2 * RING)], want_checksums=True)      # warm-up
+    sums = {}
+
+    def call():
+        # the two scenes are driven from a host thread each (a scene is single-threaded, distinct scenes are not), so
+        # their batches run side by side on the device and the checksum read-back of one does not drain the other
+        def job(name):
+            sums[name] = scenes[name].render_views(v, want_checksums=True)
+        ts = [threading.Thread(target=job, args=(name,)) for name in scenes]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+
+    ms = max_over_ranks(torch, dist, timed_batches(torch, dist, tstream, pstreams, call, 1, preroll=0))
+    mine = 0
+    for name in scenes:
+        with np.errstate(over="ignore"):
+            mine = (mine + int(sums[name].sum(dtype=np.uint64))) & 0xFFFFFFFFFFFFFFFF
+    if dist is not None:
+        parts = [None] * world
+        dist.all_gather_object(parts, mine)
+        mine = sum(parts) & 0xFFFFFFFFFFFFFFFF
+    out = {"metric": "Mpixels/s shaded (device-timed) at 7680x4320", "value": VIEWS_8K * n_px / (ms * 1e-3) / 1e6, "unit": "Mpixels/s",
+           "n_gpus": world, "scaling": "strong", "views": VIEWS_8K, "views_per_gpu": 2 * (hi - lo), "ms": ms,
+           "us_per_view": ms * 1e3 / max(1, 2 * (hi - lo)), "checksum_of_checksums": mine,
+           "config": "BASELINE config 5: african_head (views 0-%d) + diablo (views %d-%d), specular, 7680x4320, camera angle 2*pi*j/%d, "
+                     "light 0.7 rad, per-view checksums on; rank r renders views [r n/N, (r+1) n/N) of each model"
+                     % (n_per_model - 1, n_per_model, VIEWS_8K - 1, n_per_model)}
+    if rank == 0:
+        peak, _ = load_peaks()
+        cov = {}
+        for name, s in scenes.items():
+            v0 = views_8k(0, 1, n_per_model)[0]
+            s.clear(); s.set_light_direction(v0[9:12]); s.set_camera(v0[0:3], v0[3:6], v0[6:9]); s.render()
+            cov[name] = int((s.raw_visibility() != 0xFFFFFFFF).sum())
+        tri = {"african_head": len(head.tri_idx), "diablo": len(model.tri_idx)}
+        nbytes = sum(algorithmic_bytes(n_px, cov[k], tri[k], "specular")["frame"] for k in scenes) / 2
+        us = out["us_per_view"] * world          # device time per view on one GPU
+        out["roofline"] = {"bound": "hbm", "algorithmic_bytes_per_view": nbytes, "us_per_view_per_gpu": us,
+                           "achieved": nbytes / (us * 1e-6) / 1e9, "peak": peak,
+                           "unit": "GB/s", "frac": nbytes / (us * 1e-6) / 1e9 / peak, "covered_px_view0": cov,
+                           "note": "overlapped view batch (k_raster<3,128>); bytes = 19 P + 3 maps x min(3 C, 3 MiB) + geometry, C of view 0"}
+        out["covered_mpix_per_s"] = out["value"] * (sum(cov.values()) / 2) / n_px
+    for s in scenes.values():
+        s.close()
+    return out
+
+
+def run_shadow4k(rank, world, dev, model, dist, tstream, steps):
+    """BASELINE config 3: diablo, shadow pipeline (light depth pass + phong shade), 3840x2160, the 64 turntable views under
+    light angles 0.7 and 2.1 rad: one step = 128 frames through tr_scene_render_views."""
+    import torch
+    from tiny_renderer_b200.scene import Scene
+    s = Scene(W4K, H4K, model, "shadow", device=dev, ring=RING)
+    ps = torch.cuda.Stream(device=dev)
+    s.set_stream(ps.cuda_stream)
+    views = np.concatenate([view_batch(rank=rank, light_angle=0.7), view_batch(rank=rank, light_angle=2.1)])
+    s.render_views(views[:16], want_checksums=False)
+    ms = timed_batches(torch, dist, tstream, [ps], lambda: s.render_views(views, want_checksums=False), steps)
+    ms = max_over_ranks(torch, dist, ms)
+    n_px = W4K * H4K
+    out = {"metric": METRIC, "value": world * steps * len(views) * n_px / (ms * 1e-3) / 1e6, "unit": "Mpixels/s", "n_gpus": world,
+           "scaling": "weak", "frames_per_step_per_gpu": len(views), "steps": steps, "us_per_frame": ms * 1e3 / (steps * len(views)),
+           "config": "BASELINE config 3: diablo, shadow, 3840x2160, 64 camera angles x light angles {0.7, 2.1} rad"}
+    if rank == 0:
+        peak, _ = load_peaks()
+        lone = lone_frame_us(s, views[[8, 72]], reps=4)
+        diag = s.diagnostics()
+        covered = int((s.raw_visibility() != 0xFFFFFFFF).sum())
+        nbytes = algorithmic_bytes(n_px, covered, len(model.tri_idx), "shadow")["frame"]
+        frame_us = sum(lone.get(k, 0.0) for k in ("K1_vertex_setup", "K3_raster_visibility", "K4_shadow_depth"))
+        if "K1_vertex_setup" in lone:
+            frame_us += lone["K1_vertex_setup"]          # two set-up launches per frame (light, camera); the figure is per launch
+        out["lone_frame"] = {"kernel_us": lone, "us": frame_us, "algorithmic_bytes": nbytes,
+                             "frac": nbytes / (frame_us * 1e-6) / 1e9 / peak if frame_us else None,
+                             "note": "K1(light) + K4 + K1(camera) + K3/K5, 256-thread CTA shape, one frame at a time"}
+        out["roofline"] = {"bound": "hbm", "algorithmic_bytes_per_frame": nbytes, "achieved": nbytes / (out["us_per_frame"] * 1e-6) / 1e9,
+                           "peak": peak, "unit": "GB/s", "frac": nbytes / (out["us_per_frame"] * 1e-6) / 1e9 / peak,
+                           "note": "overlapped batch (k_raster<-2,128> + k_raster<5,128>); bytes = 27 P + min(3 C, 3 MiB) + geometry of both passes"}
+        out["shadow_index_oob"] = diag["shadow_index_oob"]
+    s.close()
+    return out
 
 
 def bind_to_gpu_numa_node(dev):
@@ -374,6 +624,80 @@ def bind_to_gpu_numa_node(dev):
         return None
 
 
+def run_e2e(torch, dist, rank, world, dev, scenes, views, steps):
+    """The reference-facing call with HOST destinations: tr_scene_render_views(views, frames -> host), per frame
+    clear / set_light_direction / set_camera / render + delivery of the top-down RGB8 frame, all inside the timed region
+    (wall clock around the calls, barrier + synchronize on both sides).  Each scene delivers into E2E_HOST_FRAMES pinned
+    host frames (tr_host_alloc), 16 views per call, from a host thread of its own; a host frame receives a different view
+    every time it comes round, so the damage tracking of the sparse delivery (k_host.cuh) is exercised, not bypassed."""
+    import tiny_renderer_b200 as tr
+    n_px = W4K * H4K
+    host = {p: tr.pinned_empty((E2E_HOST_FRAMES, H4K, W4K, 3), np.uint8) for p in PIPES}
+    chunks = [views[i:i + E2E_HOST_FRAMES] for i in range(0, len(views), E2E_HOST_FRAMES)]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def e2e_step():
+        def job(p):
+            for c in chunks:
+                scenes[p].render_views(c, want_checksums=False, frames_out=host[p][:len(c)])
+        ts = [threading.Thread(target=job, args=(p,)) for p in PIPES]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+
+    e2e_step()
+    for s in scenes.values():
+        s.transfer_stats(reset=True)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        e2e_step()
+    barrier()
+    secs = max_over_ranks(torch, dist, time.perf_counter() - t0)
+    st = [s.transfer_stats() for s in scenes.values()]
+    frames = steps * len(PIPES) * len(views)
+    d2h = sum(x["sparse_bytes"] + x["copied_bytes"] for x in st)
+    # exactness spot check, outside the timed region: the last delivered host frames against a plain full copy
+    exact = True
+    for p in PIPES:
+        last = chunks[-1]
+        for k in (0, len(last) - 1):
+            v = last[k]
+            s = scenes[p]
+            s.clear(); s.set_light_direction(v[9:12]); s.set_camera(v[0:3], v[3:6], v[6:9]); s.render()
+            exact = exact and bool(np.array_equal(host[p][k], s.get_frame_buffer()))
+    # What bounds e2e: the device->host link.  A plain cudaMemcpyAsync into pinned memory, all ranks at once, is the yardstick.
+    nbytes = 16 * n_px * 3
+    src = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    dst = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    dst.copy_(src, non_blocking=True)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        dst.copy_(src, non_blocking=True)
+    torch.cuda.synchronize()
+    copy_s = max_over_ranks(torch, dist, (time.perf_counter() - t0) / 3)
+    del src, dst
+    d2h_all = sum_over_ranks(torch, dist, float(d2h))
+    link = world * nbytes / copy_s / 1e9
+    ach = d2h_all / secs / 1e9
+    return {"value": world * frames * n_px / secs / 1e6, "unit": "Mpixels/s", "h2d_bytes_per_step": len(PIPES) * len(views) * 48,
+            "d2h_bytes_per_step": d2h / steps, "d2h_bytes_per_frame": d2h / frames, "full_frame_bytes": n_px * 3,
+            "frames_sparse": sum(x["frames_sparse"] for x in st), "frames_copied": sum(x["frames_copied"] for x in st),
+            "frames_exact": exact, "steps": steps, "frames_per_step_per_gpu": len(PIPES) * len(views), "seconds": secs,
+            "note": "tr_scene_render_views(views, frames -> tr_host_alloc memory): the device stores only tile rows that are non-zero "
+                    "now or were non-zero after the previous delivery to the same host frame (k_frame_to_host); the caller reads "
+                    "complete, exact top-down RGB8 frames (frames_exact: spot check against tr_scene_get_frame_buffer into ordinary "
+                    "memory, outside the timed region); inputs are the 12 floats of camera+light per frame (kernel arguments)",
+            "roofline": {"bound": "pcie d2h", "achieved": ach, "peak": link, "unit": "GB/s", "frac": ach / link,
+                         "peak_source": "plain pinned device->host copy of 16 frames, all ranks at once, measured in this run",
+                         "equivalent_full_frame_GBps": world * frames * n_px * 3 / secs / 1e9}}
+
+
 def run_gpu(args, rank, world, local_rank):
     import torch
     import tiny_renderer_b200 as tr
@@ -390,187 +714,144 @@ def run_gpu(args, rank, world, local_rank):
     # scene given the NULL stream would fall back to its own stream and escape the CUDA events below.
     tstream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(tstream)
-    stream = tstream.cuda_stream
-    assert stream != 0
+    assert tstream.cuda_stream != 0
     model, data = bench_model()
+    head, _ = bench_model("african_head")
     n_px = W4K * H4K
     n_tri = len(model.tri_idx)
-    views = view_batch(rank)
+    views = view_batch(rank=rank)
     scenes = {p: Scene(W4K, H4K, model, p, device=dev, ring=RING) for p in PIPES}
     # The two scenes of the step are independent objects (one pipeline per Scene, as in the reference), so each is
     # driven on a stream of its own: their view batches run side by side instead of draining one before the other
-    # starts.  Both streams are fenced by the timing events on the main stream (fork() / join() below).
+    # starts.  Both streams are fenced by the timing events on the main stream (timed_batches).
     pstreams = {p: torch.cuda.Stream(device=dev) for p in PIPES}
     for p in PIPES:
         scenes[p].set_stream(pstreams[p].cuda_stream)
 
-    def fork():
-        for ps in pstreams.values():
-            ps.wait_stream(tstream)
+    def make_step(v, reps):
+        def step():
+            for _ in range(reps):
+                for p in PIPES:
+                    scenes[p].render_views(v, want_checksums=False)
+        return step
 
-    def join():
-        for ps in pstreams.values():
-            tstream.wait_stream(ps)
-
-    def step():
-        for p in PIPES:
-            scenes[p].render_views(views, want_checksums=False)
-
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
+    step = make_step(views, REPS)
     for _ in range(max(args.warmup, 3)):
         step()
     for s in scenes.values():
         s.kernel_times()                      # reset launch counters
     sampler = ClockSampler(dev)          # every rank samples its own GPU: `value` is set by the slowest one
     sampler.start()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    # Two more untimed steps behind the barrier, joined before e0: the device has drained them when the timed steps
-    # start, but the host has long since queued the timed steps behind them.  Without this the first timed launches
-    # are fed by a host thread that has just left the barrier; with 8 ranks on one host a single late wake-up showed
-    # up as 10 % of a 20-step (9 ms) region on one rank — and `value` is the slowest rank's.
-    fork()
-    for _ in range(PREROLL_STEPS):
-        step()
-    join()
-    e0.record()
-    fork()
-    for _ in range(args.steps):
-        step()
-    join()
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
+    ms = timed_batches(torch, dist, tstream, list(pstreams.values()), step, args.steps, preroll=PREROLL_STEPS)
     clocks = sampler.stop()
     launches = sum(n for s in scenes.values() for (_, n) in s.kernel_times().values())
+    launches = launches * args.steps // (args.steps + PREROLL_STEPS)         # the pre-roll step is outside the events
     if dist is not None:
         per_rank = [None] * world
         dist.all_gather_object(per_rank, {"rank": rank, "ms_per_step": ms / args.steps, "sm_mhz": clocks["sm_mhz"], "reasons": clocks["reasons"]})
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        ms = max_over_ranks(torch, dist, ms)
         # the line's clocks describe the whole job: lowest median clock and every throttle reason any rank saw
         mhz = [r["sm_mhz"] for r in per_rank if r["sm_mhz"]]
         clocks = dict(clocks, sm_mhz=min(mhz) if mhz else None, reasons=sorted({x for r in per_rank for x in r["reasons"]}), per_rank=per_rank)
-    frames_per_step = len(PIPES) * N_ANGLES
+    frames_per_step = len(PIPES) * N_ANGLES * REPS
     value = world * args.steps * frames_per_step * n_px / (ms * 1e-3) / 1e6
 
-    # ---- e2e: the reference-facing calls with a HOST destination, D2H inside the timed region ----
-    # One pinned host buffer per frame of the step: tr_scene_render_views copies every finished frame to the host
-    # (asynchronously, on the frame's own stream, so copies overlap the next frames' rendering) and returns when
-    # all of them have landed.
-    host = tr.pinned_empty((len(PIPES), N_ANGLES, H4K, W4K, 3), np.uint8)
-    def e2e_step():
-        for i, p in enumerate(PIPES):
-            scenes[p].render_views(views, want_checksums=False, frames_out=host[i])
-    e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    e2e_steps = max(1, min(args.steps, 3))
-    for _ in range(e2e_steps):
-        e2e_step()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    if dist is not None:
-        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e_value = world * e2e_steps * frames_per_step * n_px / e2e_s / 1e6
-    # What bounds e2e: the device->host link.  A plain cudaMemcpyAsync of one step's frame bytes into pinned memory,
-    # timed the same way, is the yardstick (rank 0, single-GPU runs only: ranks of one box share the host's link).
-    pcie = None
-    if rank == 0 and world == 1:
-        nbytes = frames_per_step * n_px * 3
-        src = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-        dst = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
-        dst.copy_(src, non_blocking=True)
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(3):
-            dst.copy_(src, non_blocking=True)
-        torch.cuda.synchronize()
-        copy_s = (time.perf_counter() - t0) / 3
-        del src, dst
-        pcie = {"bound": "pcie d2h", "achieved": nbytes * e2e_steps / e2e_s / 1e9, "peak": nbytes / copy_s / 1e9, "unit": "GB/s",
-                "frac": (nbytes * e2e_steps / e2e_s) / (nbytes / copy_s),
-                "peak_source": "plain pinned device->host copy of one step's frame bytes, measured in this run"}
+    # the r1 workload once, for comparison: 8 angles on 8 slots, every slot re-renders the same frame (no tile-state flips)
+    v8 = view_batch(8, rank)
+    step8 = make_step(v8, 8 * REPS)
+    step8()
+    ms8 = max_over_ranks(torch, dist, timed_batches(torch, dist, tstream, list(pstreams.values()), step8, 3))
+    aliased = world * 3 * len(PIPES) * 8 * 8 * REPS * n_px / (ms8 * 1e-3) / 1e6
+
+    e2e = run_e2e(torch, dist, rank, world, dev, scenes, views, max(2, min(args.steps, 10)))
+    e2e["host_numa_node"] = numa_node
 
     line = {"metric": METRIC, "value": value, "unit": "Mpixels/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": data, "config": workload_config(),
-            "e2e": {"value": e2e_value, "unit": "Mpixels/s", "h2d_bytes_per_step": frames_per_step * 48,
-                    "d2h_bytes_per_step": frames_per_step * n_px * 3,
-                    "note": "tr_scene_render_views(views, frames -> pinned host): per frame clear/set_light_direction/set_camera/"
-                            "render + device->host copy of the RGB8 frame, all inside the timed region; inputs are the 12 "
-                            "floats of camera+light per frame (kernel arguments); PCIe-bound: 24.9 MB per frame",
-                    "host_numa_node": numa_node, "roofline": pcie},
-            "gpu_launches": int(launches), "clocks": clocks}
+            "timed_region_ms": ms, "aliased_8_angles": {"value": aliased, "unit": "Mpixels/s",
+                                                        "note": "r1's workload: 8 angles on 8 frame slots, each slot re-renders the identical frame"},
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
 
     if rank == 0:
+        # ---- coverage of the 64 views (light-independent; identical for both pipelines) ----
+        s = scenes["phong"]
+        cov = []
+        for v in views:
+            s.clear(); s.set_light_direction(v[9:12]); s.set_camera(v[0:3], v[3:6], v[6:9]); s.render()
+            cov.append(int((s.raw_visibility() != 0xFFFFFFFF).sum()))
+        mean_cov = float(np.mean(cov))
+        line["covered_mpix_per_s"] = value * mean_cov / n_px
+        line["covered_fraction"] = mean_cov / n_px
         # ---- roofline of the dominant kernel: per-kernel CUDA events (profiling mode), separate from `value` ----
         peak, peak_src = load_peaks()
+        n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+        sm_mhz = clocks.get("sm_mhz")
+        sample = views[::8]                                  # 8 of the 64 angles
         per = {}
-        covered = {}
         for p in PIPES:
             s = scenes[p]
-            # untimed first launch: the lone-frame CTA shape of the tile kernel has not run yet in this process, and
-            # lazy module loading would otherwise land in the first timed launch
-            v = views[0]
-            s.clear(); s.set_light_direction(v[9:12]); s.set_camera(v[0:3], v[3:6], v[6:9]); s.render(); s.synchronize()
-            s.set_profiling(True)
-            s.kernel_times()
-            # one frame at a time on one stream (no overlap between frames): the kernel's own duration
-            for _ in range(3):
-                for v in views:
-                    s.clear(); s.set_light_direction(v[9:12]); s.set_camera(v[0:3], v[3:6], v[6:9]); s.render()
-            kt = s.kernel_times()
-            s.set_profiling(False)
-            covered[p] = int((s.raw_visibility() != 0xFFFFFFFF).sum())
-            per[p] = {k: (t / n * 1e3 if n and t > 0 else 0.0) for k, (t, n) in kt.items() if n and t > 0}     # us per launch
+            per[p] = {"256": lone_frame_us(s, sample)}
+            s.set_debug_flags(2)                             # lone frames in the batch CTA shape (128 threads)
+            per[p]["128"] = lone_frame_us(s, sample)
+            s.set_debug_flags(0)
         line["kernel_us"] = per
-        best = None
-        for p in PIPES:
-            ab = algorithmic_bytes(n_px, covered[p], n_tri, p)
-            frame_us = sum(per[p].get(k, 0.0) for k in ("K1_vertex_setup", "K3_raster_visibility"))
-            for k in ("K3_raster_visibility",):
-                us = per[p].get(k, 0.0)
-                if best is None or us > best[0]:
-                    best = (us, p, k, ab[k], ab["frame"], frame_us)
-        us, p, k, nbytes, frame_bytes, frame_us = best
-        achieved = nbytes / (us * 1e-6) / 1e9
-        line["roofline"] = {"bound": "hbm", "kernel": "k_raster<%s> = K3 raster_visibility + K5 shade fused" % p, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                            "frac": achieved / peak, "traffic": ncu_traffic(p), "peak_source": peak_src,
-                            "algorithmic_bytes_per_launch": nbytes, "us_per_launch": us,
-                            "note": "kernel timed one frame at a time (CUDA events on the launching stream, profiling mode); "
-                                    "`batch` is the same byte count over the overlapped view batch of the timed region",
-                            "frame_serial": {"algorithmic_bytes": frame_bytes, "us": frame_us,
-                                             "achieved": frame_bytes / (frame_us * 1e-6) / 1e9,
-                                             "frac": frame_bytes / (frame_us * 1e-6) / 1e9 / peak},
-                            "batch": batch_roofline(ms / args.steps / frames_per_step * 1e3, n_px, covered, n_tri, peak)}
-        n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
-        # the same kernel and the whole overlapped batch against the instruction-issue / FP32 rate (what actually binds them)
-        line["roofline"]["issue"] = issue_roofline(["k_raster<%d,256>" % {"phong": 1, "darboux": 4}[p]], us, n_sm, clocks.get("sm_mhz"))
-        line["roofline"]["batch"]["issue"] = issue_roofline(["k_raster<1,128>", "k_raster<4,128>", "k_vertex_setup<0>", "k_vertex_setup<0>"],
-                                                            2 * ms / args.steps / frames_per_step * 1e3, n_sm, clocks.get("sm_mhz"))
-        if world == 1:
+        cov8 = float(np.mean(cov[::8]))
+        ab = {p: algorithmic_bytes(n_px, cov8, n_tri, p) for p in PIPES}
+        dom = "darboux"                                      # the slower pipeline: its tile kernel dominates the step
+
+        def kernel_fig(p, shape):
+            us = per[p][shape].get("K3_raster_visibility", 0.0)
+            nb = ab[p]["K3_raster_visibility"]
+            e = ncu_kernel_summary("k_raster<%d,%s>" % (PIPE_ID[p], shape))
+            return {"kernel": "k_raster<%s,%s>" % (p, shape), "cta_threads": int(shape), "us_per_launch": us, "algorithmic_bytes_per_launch": nb,
+                    "achieved": nb / (us * 1e-6) / 1e9 if us else None, "frac": nb / (us * 1e-6) / 1e9 / peak if us else None,
+                    "traffic": e["dram_bytes_per_launch"] if e else None,
+                    "issue": issue_roofline(["k_raster<%d,%s>" % (PIPE_ID[p], shape)], us, n_sm, sm_mhz) if us else None}
+
+        def frame_fig(p, shape):
+            us = sum(per[p][shape].get(k, 0.0) for k in ("K1_vertex_setup", "K3_raster_visibility"))
+            return {"cta_threads": int(shape), "algorithmic_bytes": ab[p]["frame"], "us": us,
+                    "achieved": ab[p]["frame"] / (us * 1e-6) / 1e9, "frac": ab[p]["frame"] / (us * 1e-6) / 1e9 / peak}
+
+        k = kernel_fig(dom, "128")
+        batch_bytes = sum(ab[p]["frame"] for p in PIPES) / len(PIPES)
+        us_frame = ms / args.steps / frames_per_step * 1e3
+        table, tsrc = ncu_summaries()
+        steady = table.get("batch_steady_state") if isinstance(table, dict) else None
+        line["roofline"] = {
+            "bound": "hbm", "kernel": k["kernel"] + " = K3 raster_visibility + K5 shade fused, the CTA shape that runs in the timed region, timed one frame at a time",
+            "achieved": k["achieved"], "peak": peak, "unit": "GB/s", "frac": k["frac"], "peak_source": peak_src,
+            "traffic": (steady or {}).get("dram_bytes_per_frame", k["traffic"]),
+            "traffic_source": ("%s: dram__bytes summed over %s consecutive tile-kernel launches of the de-aliased overlapped batch / frames"
+                               % (tsrc, (steady or {}).get("launches"))) if steady else "per-launch ncu capture of this kernel (serialised)",
+            "algorithmic_bytes_per_launch": k["algorithmic_bytes_per_launch"], "us_per_launch": k["us_per_launch"], "issue": k["issue"],
+            "kernels": {p + "," + sh: kernel_fig(p, sh) for p in PIPES for sh in ("128", "256")},
+            "frame_serial": dict(frame_fig(dom, "256"), note="lone darboux frame K1 + K3/K5, 256-thread shape (what tr_scene_render launches)"),
+            "frame_serial_phong": frame_fig("phong", "256"),
+            "batch": {"algorithmic_bytes_per_frame": batch_bytes, "us_per_frame": us_frame, "achieved": batch_bytes / (us_frame * 1e-6) / 1e9,
+                      "frac": batch_bytes / (us_frame * 1e-6) / 1e9 / peak,
+                      "note": "the timed region: both pipelines' frames overlapped, 128-thread shape",
+                      "issue": issue_roofline(["k_raster<1,128>", "k_raster<4,128>", "k_vertex_setup<0>", "k_vertex_setup<0>"],
+                                              2 * us_frame, n_sm, sm_mhz)}}
+        if world == 1 and not QUICK:
             # what a rasteriser resolving visibility with global 64-bit atomicMin could reach on this box
-            # (distinct addresses, every atomic updates, one atomic per fragment); k_raster resolves in registers instead
             rate = tr.bench_atomic_min(W4K, H4K, rounds=4, repeats=3, device=dev)
             line["atomic_min_peak"] = {"atomics_per_s": rate, "equivalent_GB_per_s": rate * 8 / 1e9,
                                        "us_per_4k_depth_layer": n_px / rate * 1e6,
                                        "note": "micro-benchmark only (tr_bench_atomic_min); not on the render path"}
-            line["cpu_baseline"] = cpu_baseline(model)
-            ao_cpu = cpu_ao_baseline(model, 3, 1)
     for s in scenes.values():
         s.close()
-    line["ao"] = run_ao(args, rank, world, dev, model, dist, stream, sm_mhz=(clocks or {}).get("sm_mhz") if rank == 0 else None)
-    if rank == 0 and world == 1:
-        line["ao"]["cpu_baseline"] = ao_cpu
+    sm_mhz0 = (clocks or {}).get("sm_mhz") if rank == 0 else None
+    line["shadow4k"] = run_shadow4k(rank, world, dev, model, dist, tstream, max(2, min(args.steps, 10)))
+    line["ao"] = run_ao(args, rank, world, dev, model, dist, tstream, sm_mhz=sm_mhz0)
+    line["views8k"] = run_views8k(rank, world, dev, model, head, dist, tstream)
+    if rank == 0 and world == 1 and not QUICK:
+        cpu = cpu_baselines(model, head)
+        line["cpu_baseline"] = cpu["main"]
+        line["shadow4k"]["cpu_baseline"] = cpu["shadow4k"]
+        line["ao"]["cpu_baseline"] = cpu["ao"]
+        line["views8k"]["cpu_baseline"] = cpu["views8k"]
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:
@@ -581,7 +862,7 @@ def run_gpu(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="tinyr", choices=["tinyr", "reference"])
     args = ap.parse_args()
