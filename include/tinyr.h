@@ -94,6 +94,10 @@ int tr_scene_diagnostics(tr_scene* s, uint64_t out[8]);
 /* The uniforms of the last prepare (shader.rs:183-279), row-major 4x4: vpmv, i_vpmv, m, i_m, it_m, shadow,
  * then camera_direction[3], t_light_direction[3] — 102 floats. */
 int tr_scene_get_uniforms(tr_scene* s, float out[102]);
+/* The constants K0 hoists out of the shadow / occlusion fragments (shader.rs:763-764, 899-900, 916-929): out[0..48) the 16
+ * occlusion sample offsets rot * (sin a_k, 0, cos a_k) * 0.02 (xyz each; occlusion pipeline only), out[48..64)
+ * shadow_matrix * i_vpmv, row-major. */
+int tr_scene_get_ao_uniforms(tr_scene* s, float out[64]);
 
 /* ---- batch modes (BASELINE.json configs 4 and 5) -------------------------------------------------------- */
 typedef struct tr_view {

@@ -573,6 +573,26 @@ void orc_scene_uniforms(void* h, float* out) {
     out[99] = b.t_light_direction.x; out[100] = b.t_light_direction.y; out[101] = b.t_light_direction.z;
 }
 
+// The per-pass constants of the occlusion fragment (shader.rs:882-885, 899-900, 916-929) as the reference recomputes them
+// for every fragment: out[0..48) = the 16 sample offsets dir_k * 0.02 (xyz each), out[48..64) = shadow_matrix * i_vpmv
+// (column-major).  Returns 1 where the reference would panic (light w != 0, rotation_between None).
+int orc_scene_ao_uniforms(void* h, float* out) {
+    Buffer& b = ((Scene*)h)->buffer;
+    V3 light;
+    if (!vector_from_h(mul(b.i_m_matrix, vector_h(b.t_light_direction)), &light)) return 1;
+    M3 rot;
+    if (!rotation_between(V3{0.0f, 0.0f, 1.0f}, light, &rot)) return 1;
+    const float angle_coef = (2.0f * 3.14159265358979323846f) / 16.0f;
+    for (int i = 0; i < 16; ++i) {
+        float a = angle_coef * (float)i;
+        V3 d = scale(mul(rot, V3{std::sin(a), 0.0f, std::cos(a)}), 0.02f);
+        out[3 * i] = d.x; out[3 * i + 1] = d.y; out[3 * i + 2] = d.z;
+    }
+    M4 sm = mul(b.shadow_matrix, b.i_vpmv_matrix);
+    std::memcpy(out + 48, sm.m, 64);
+    return 0;
+}
+
 // Many-light ambient-occlusion batch (BASELINE.json config 4; semantics SURVEY.md §8(d)): for each light
 // `set_light_direction; clear; render` with the scene's (occlusion) pipeline, accum[p] += gray (u32), where
 // p is the bottom-up pixel index and gray is channel 0 of the frame the reference would have produced.

@@ -50,6 +50,8 @@ def lib():
                      "orc_scene_diagnostics", "orc_scene_uniforms"):
             getattr(L, name).argtypes = [ctypes.c_void_p, ctypes.c_void_p]
             getattr(L, name).restype = None
+        L.orc_scene_ao_uniforms.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.orc_scene_ao_uniforms.restype = ctypes.c_int
         L.orc_scene_render_ao.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p]
         L.orc_scene_render_ao.restype = ctypes.c_int
         _LIB = L
@@ -140,6 +142,13 @@ class OracleScene:
         out["camera_direction"] = u[96:99].copy()
         out["t_light_direction"] = u[99:102].copy()
         return out
+
+    def ao_uniforms(self):
+        """Per-pass constants of the occlusion fragment: 16 sample offsets (16, 3) and shadow * i_vpmv ([r][c])."""
+        u = np.empty(64, np.float32)
+        if lib().orc_scene_ao_uniforms(self._h, u.ctypes.data):
+            raise RuntimeError("reference would panic in the occlusion fragment's set-up")
+        return {"ao_step": u[:48].reshape(16, 3).copy(), "shadow_from_screen": u[48:].reshape(4, 4).T.copy()}
 
     def render_ao(self, light_dirs, accum=None):
         lights = np.ascontiguousarray(light_dirs, np.float32).reshape(-1, 3)

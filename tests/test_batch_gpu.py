@@ -417,3 +417,28 @@ def test_sparse_host_frames_geometry_change_and_4k(tinyr):
     st = b.transfer_stats()
     assert st["frames_sparse"] == 2 and st["sparse_bytes"] < 1.5 * 3840 * 2160 * 3     # first one whole, second sparse
     a.close(); b.close()
+
+
+def test_config4_render_ao_at_4k_matches_oracle(tinyr, oracle):
+    """BASELINE config 4 at its REAL size: tr_scene_render_ao at 3840x2160 (1.5 M-pixel compaction list, 4080-tile depth
+    passes overlapped on 8 slots) for 4 lights of the committed fixture == the oracle's sum of its own occlusion frames,
+    bit for bit; no shadow lookup leaves the buffer.  Also with the range-tested sample form forced (debug bit 0)."""
+    from tiny_renderer_b200.scene import Scene
+    m = get_model("diablo")
+    if m.name != "diablo":
+        pytest.skip("reference assets not staged")
+    lights = np.load(os.path.join(HERE, "golden", "ao_lights_diablo_1024.npy"))[[0, 341, 682, 1023]]
+    lf, la, up, _ = assets.view_vectors(0.0, 0.0)
+    o = oracle.OracleScene(3840, 2160, m, "occlusion")
+    o.set_camera(lf, la, up)
+    want = o.render_ao(lights)
+    assert o.diagnostics()["shadow_index_oob"] == 0
+    for ring, flags in ((8, 0), (1, 0), (8, 1)):
+        g = Scene(3840, 2160, m, "occlusion", ring=ring)
+        g.set_debug_flags(flags)
+        g.set_camera(lf, la, up)
+        got = g.render_ao(lights)
+        assert np.array_equal(got, want), (ring, flags, int((got != want).sum()))
+        d = g.diagnostics()
+        assert d["shadow_index_oob"] == 0 and d["shadow_x_wrap"] == 0
+        g.close()

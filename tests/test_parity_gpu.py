@@ -379,3 +379,42 @@ def test_tile_list_exactly_full(tinyr, oracle, batch_shape):
                 st = parity.compare(g, o, rgb_frac=1.0)
                 assert st["rgb_exact_frac"] == 1.0 and st["depth_bits_differ"] == 0, (n_in, n_out, pipeline, rep, st)
                 g.close()
+
+
+@pytest.mark.parametrize("pipeline", PIPELINES)
+def test_k0_uniforms_equal_the_oracle_bit_for_bit(tinyr, oracle, pipeline):
+    """K0 (csrc/tr_prepare.h) against the oracle's prepare functions directly, not through colours: vpmv, i_vpmv, m, i_m,
+    it_m, the light matrix, camera_direction, t_light_direction — and for the two-pass pipelines the constants K0 hoists
+    out of the fragment stage (shadow_matrix * i_vpmv; the 16 occlusion sample offsets, shader.rs:916-929)."""
+    from tiny_renderer_b200.scene import Scene
+    model = get_model("african_head")
+    rng = np.random.default_rng(99)
+    for w, h in ((800, 800), (3840, 2160), (333, 201)):
+        g = Scene(w, h, model, pipeline)
+        o = oracle.OracleScene(w, h, model, pipeline)
+        for trial in range(4):
+            if trial == 0:
+                lf, la, up, light = assets.view_vectors(0.9, 0.7)
+            else:
+                d = rng.normal(size=3); d /= np.linalg.norm(d)
+                lf = (d * rng.uniform(0.5, 2.5)).astype(np.float32)
+                la = rng.uniform(-0.3, 0.3, 3).astype(np.float32)
+                up = np.array([rng.uniform(-0.2, 0.2), 1.0, rng.uniform(-0.2, 0.2)], np.float32)
+                l = rng.normal(size=3)
+                light = (l / np.linalg.norm(l)).astype(np.float32)
+            o.clear(); o.set_light_direction(light); o.set_camera(lf, la, up)
+            if o.render(allow_panic=True):
+                continue
+            parity.drive(g, lf, la, up, light)
+            gu, ou = g.uniforms(), o.uniforms()
+            names = ["vpmv", "m", "it_m", "camera_direction", "t_light_direction"]
+            if pipeline in TWO_PASS:
+                names += ["i_vpmv", "i_m", "shadow"]
+            for n in names:
+                assert np.array_equal(gu[n].view(np.uint32), ou[n].view(np.uint32)), (w, h, trial, n, gu[n], ou[n])
+            if pipeline in TWO_PASS:
+                ga, oa = g.ao_uniforms(), o.ao_uniforms()
+                assert np.array_equal(ga["shadow_from_screen"].view(np.uint32), oa["shadow_from_screen"].view(np.uint32)), (w, h, trial)
+                if pipeline == "occlusion":
+                    assert np.array_equal(ga["ao_step"].view(np.uint32), oa["ao_step"].view(np.uint32)), (w, h, trial)
+        g.close()

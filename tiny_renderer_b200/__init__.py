@@ -91,7 +91,7 @@ def lib():
             "tr_scene_get_frame_buffer": [vp, vp], "tr_scene_get_z_buffer": [vp, vp], "tr_scene_get_shadow_buffer": [vp, vp],
             "tr_scene_read_frame_raw": [vp, vp], "tr_scene_read_depth": [vp, vp], "tr_scene_read_shadow": [vp, vp],
             "tr_scene_read_visibility": [vp, vp], "tr_scene_set_pipeline": [vp, ctypes.c_char_p],
-            "tr_scene_diagnostics": [vp, vp], "tr_scene_get_uniforms": [vp, vp],
+            "tr_scene_diagnostics": [vp, vp], "tr_scene_get_uniforms": [vp, vp], "tr_scene_get_ao_uniforms": [vp, vp],
             "tr_scene_render_views": [vp, vp, u32, vp, vp], "tr_scene_render_ao": [vp, vp, u32, i32, vp],
             "tr_scene_ao_device_buffer": [vp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)], "tr_scene_read_ao": [vp, vp],
             "tr_scene_ao_ipc_handle": [vp, vp], "tr_scene_ao_open_peers": [vp, vp, u32, u32],

@@ -701,6 +701,16 @@ int tr_scene_get_uniforms(tr_scene* s, float out[102]) {
     return TR_OK;
 }
 
+// The hoisted per-fragment constants of the shadow / occlusion fragments (tr_prepare.h), for parity tests against the
+// values the reference recomputes per fragment.
+int tr_scene_get_ao_uniforms(tr_scene* s, float out[64]) {
+    NEED(s);
+    if (!out) return fail(TR_ERR_INVALID_ARGUMENT, "null destination");
+    for (int k = 0; k < 16; ++k) { out[3 * k] = s->uni.ao_step[k].x; out[3 * k + 1] = s->uni.ao_step[k].y; out[3 * k + 2] = s->uni.ao_step[k].z; }
+    memcpy(out + 48, s->uni.shadow_from_screen.m, 64);
+    return TR_OK;
+}
+
 int tr_scene_set_debug_flags(tr_scene* s, uint32_t flags) {
     NEED(s);
     s->debug_flags = flags;

@@ -227,6 +227,11 @@ class Scene:
         out["t_light_direction"] = u[99:102].copy()
         return out
 
+    def ao_uniforms(self):
+        """Hoisted constants of the shadow / occlusion fragments (tr_scene_get_ao_uniforms)."""
+        u = self._read("tr_scene_get_ao_uniforms", (64,), np.float32)
+        return {"ao_step": u[:48].reshape(16, 3).copy(), "shadow_from_screen": u[48:].reshape(4, 4).copy()}
+
     def render_views(self, views, want_checksums=True, frames_out=None):
         """views: (n, 12) f32 rows look_from, look_at, up, light_direction.  Returns u64 checksums (or None)."""
         v = np.ascontiguousarray(views, np.float32).reshape(-1, 12)
