@@ -89,17 +89,17 @@ impl Scene {
     pub fn render(&mut self) -> Result<(), Error> { check(unsafe { tr_scene_render(self.h) }) }                      // scene.rs:151
     /// get_frame_buffer (scene.rs:92): RGB8, top-down, width*height*3 bytes (wrap in image::RgbImage::from_raw).
     pub fn get_frame_buffer(&self) -> Result<Vec<u8>, Error> {
-        let mut v = vec![0u8; (self.width * self.height * 3) as usize];
+        let mut v = vec![0u8; self.width as usize * self.height as usize * 3];
         check(unsafe { tr_scene_get_frame_buffer(self.h, v.as_mut_ptr()) })?;
         Ok(v)
     }
     pub fn get_z_buffer(&mut self) -> Result<Vec<u8>, Error> {                                                        // scene.rs:101
-        let mut v = vec![0u8; (self.width * self.height * 3) as usize];
+        let mut v = vec![0u8; self.width as usize * self.height as usize * 3];
         check(unsafe { tr_scene_get_z_buffer(self.h, v.as_mut_ptr()) })?;
         Ok(v)
     }
     pub fn get_shadow_buffer(&mut self) -> Result<Vec<u8>, Error> {                                                   // scene.rs:115
-        let mut v = vec![0u8; (self.width * self.height * 3) as usize];
+        let mut v = vec![0u8; self.width as usize * self.height as usize * 3];
         check(unsafe { tr_scene_get_shadow_buffer(self.h, v.as_mut_ptr()) })?;
         Ok(v)
     }

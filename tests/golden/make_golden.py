@@ -48,10 +48,22 @@ def run_case(case):
     s.clear(); s.set_light_direction(l); s.set_camera(lf, la, up); s.render()
     vis = s.raw_visibility()
     out = {"case": list(case), "covered": int((vis != 0xFFFFFFFF).sum()), "visibility": sha(vis), "depth": sha(s.raw_z()),
-           "frame_topdown": sha(s.get_frame_buffer()), "diagnostics": s.diagnostics()}
+           "frame_topdown": sha(s.get_frame_buffer()), "diagnostics": s.diagnostics(),
+           # what the reference's own public getters return (scene.rs:101-125): the hashes rust/pin_oracle prints
+           "z_gray": sha(s.get_z_buffer()), "shadow_gray": sha(s.get_shadow_buffer())}
     if pipeline in ("shadow", "occlusion"):
         out["shadow"] = sha(s.raw_shadow())
     return out
+
+
+def write_pin_cases(path):
+    """rust/pin_oracle/cases.txt: the golden cases with camera / light vectors as f32 bit patterns."""
+    with open(path, "w") as f:
+        f.write("# asset pipeline width height look_from(3) look_at(3) up(3) light(3) as f32 bit patterns (hex); written by tests/golden/make_golden.py\n")
+        for asset, pipeline, w, h, cam, light in CASES:
+            lf, la, up, l = assets.view_vectors(cam, light)
+            words = np.concatenate([lf, la, up, l]).astype(np.float32).view(np.uint32)
+            f.write("%s %s %d %d %s\n" % (asset, pipeline, w, h, " ".join("%08x" % x for x in words)))
 
 
 if __name__ == "__main__":
@@ -60,6 +72,7 @@ if __name__ == "__main__":
         json.dump(res, f, indent=1)
     for r in res:
         print(r["case"], r["covered"], r["frame_topdown"][:12])
+    write_pin_cases(os.path.join(os.path.dirname(os.path.dirname(HERE)), "rust", "pin_oracle", "cases.txt"))
     # config 4 light set: the accepted directions are part of the fixture
     import tiny_renderer_b200 as tr  # noqa: E402  (host-only entry point: no GPU needed)
     lights, drawn = tr.generate_ao_lights(assets.load_model_py("diablo").positions, 1024)

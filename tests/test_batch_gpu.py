@@ -46,6 +46,9 @@ def test_golden_fixtures(tinyr, entry):
         assert sha(g.get_frame_buffer()) == entry["frame_topdown"]
     if "shadow" in entry:
         assert sha(g.raw_shadow()) == entry["shadow"]
+    # the reference's own getters (scene.rs:101-125): what rust/pin_oracle hashes on the Rust side
+    assert sha(g.get_z_buffer()) == entry["z_gray"]
+    assert sha(g.get_shadow_buffer()) == entry["shadow_gray"]
     d = g.diagnostics()
     for k in ("shadow_index_oob", "shadow_x_wrap", "texel_oob", "nan_depth"):
         assert d[k] == entry["diagnostics"][k]

@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <charconv>
 #include <string>
 #include <vector>
 
@@ -44,10 +45,13 @@ static bool read_file(const char* path, std::vector<uint8_t>* out) {
 
 static bool parse_f32(const std::string& s, float* v) {
     if (s.empty()) return false;
-    char* end = nullptr;
-    errno = 0;
-    *v = strtof(s.c_str(), &end);   // correctly rounded, like Rust's str::parse::<f32>
-    return end && *end == '\0';
+    // std::from_chars: correctly rounded like Rust's str::parse::<f32>, and independent of the host application's
+    // locale (strtof reads the decimal point from setlocale).  Rust accepts one leading '+', from_chars does not.
+    const char* b = s.data();
+    const char* e = b + s.size();
+    if (*b == '+' && e - b > 1 && b[1] != '-' && b[1] != '+') ++b;
+    const std::from_chars_result r = std::from_chars(b, e, *v, std::chars_format::general);
+    return r.ec == std::errc() && r.ptr == e;
 }
 
 // One face corner: "p", "p/t", "p//n" or "p/t/n"; returns a bitmask 1 (p) | 2 (t) | 4 (n), 0 on error.

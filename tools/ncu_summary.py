@@ -6,7 +6,10 @@ writes profiles/<tag>_ncu_full.csv (one row per captured launch, the raw page fi
 issue / stall metrics) and profiles/<tag>_traffic.json (per kernel: launches, DRAM bytes per launch =
 dram__bytes_read.sum + dram__bytes_write.sum, duration under ncu, warp instructions).  bench.py reads
 `roofline.traffic` from the newest *_traffic.json.  Also prints a launch-list share table when
-gpurun_out/<tag>_launches.csv exists.
+gpurun_out/<tag>_launches.csv exists, and — when gpurun_out/<tag>_steady.csv exists (dram__bytes per launch over a long
+run of consecutive tile-kernel launches of the de-aliased, ring-rotating view batch, `--cache-control none`, so L2
+contents carry over from launch to launch as they do in the timed region) — adds `batch_steady_state`: DRAM bytes per
+frame in steady state.
 """
 import collections
 import csv
@@ -79,6 +82,29 @@ def main():
         n = d["launches"]
         traffic[name] = {"launches": n, "dram_bytes_per_launch": d["dram"] / n,
                          "us_per_launch_under_ncu": d["us"] / n, "warp_instructions": d["inst"] / n}
+    steady = os.path.join(ROOT, "gpurun_out", f"{tag}_steady.csv")
+    if os.path.exists(steady):
+        lines = [ln for ln in open(steady, errors="replace") if ln.startswith('"')]
+        per_id = collections.OrderedDict()
+        for r in csv.DictReader(io.StringIO("".join(lines))):
+            m = r.get("Metric Name", "")
+            v = num(r.get("Metric Value", "")) or 0.0
+            e = per_id.setdefault(r["ID"], {"name": r["Kernel Name"], "dram": 0.0, "us": 0.0})
+            if m.startswith("dram__bytes"):
+                e["dram"] += v * BYTES.get(r.get("Metric Unit", "byte"), 1.0)
+            elif m == "gpu__time_duration.sum":
+                e["us"] += v * TIME_US.get(r.get("Metric Unit", "us"), 1.0)
+        rows = list(per_id.values())
+        if rows:
+            names = collections.Counter(e["name"].split("(")[0] for e in rows)
+            traffic["batch_steady_state"] = {
+                "launches": len(rows), "frames": len(rows), "kernels": dict(names),
+                "dram_bytes_per_frame": sum(e["dram"] for e in rows) / len(rows),
+                "dram_bytes_min_max": [min(e["dram"] for e in rows), max(e["dram"] for e in rows)],
+                "us_per_launch_under_ncu": sum(e["us"] for e in rows) / len(rows),
+                "how": "ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --cache-control none "
+                       "--clock-control none -k regex:k_raster over consecutive tile-kernel launches of the 64-angle view batch "
+                       "(8 frame slots per scene; one launch = one frame)"}
     with open(os.path.join(ROOT, "profiles", f"{tag}_traffic.json"), "w") as f:
         json.dump(traffic, f, indent=1)
     print(json.dumps(traffic, indent=1))
