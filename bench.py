@@ -313,25 +313,49 @@ def ncu_summaries():
         return json.load(f), os.path.basename(found[-1])
 
 
+PIPE_STRUCT = {"default": "PipelineDefault", "phong": "PipelinePhong", "normal_map": "PipelineNormalMap", "specular": "PipelineSpecular",
+               "darboux": "PipelineDarboux", "shadow": "PipelineShadow", "occlusion": "PipelineOcclusion",
+               "light_depth": "PassLightDepth", "visibility": "PassVisibility"}
+LEGACY_ID = dict(PIPE_ID, light_depth=-2, visibility=-1)
+
+
+def raster_kernel(pipe, threads):
+    """Name of the tile kernel instantiated with `pipe`'s fragment role (pipeline.cuh) in a CTA shape."""
+    return "k_raster<%s,%s>" % (PIPE_STRUCT[pipe], threads)
+
+
+def setup_kernel(pipe):
+    return "k_vertex_setup<%s>" % PIPE_STRUCT[pipe]
+
+
 def ncu_kernel_summary(want):
-    """Entry of the kernel whose name contains `want` (DRAM bytes, duration and warp instructions per launch)."""
-    # "k_raster<4,128>" matches ncu's spellings "k_raster<4, 128>" and "k_raster<(int)4, (int)128>"
-    def norm(name):
-        return name.replace("(int)", "").replace(" ", "")
+    """Entry of the kernel whose name contains `want` (DRAM bytes, duration and warp instructions per launch).  Also finds
+    captures taken before the kernels were templated on pipeline structs (r1: k_raster<4,128>, k_vertex_setup<0>)."""
+    def norm(name):     # ncu spells "k_raster<tr::PipelineDarboux, 128>" / "k_raster<(int)4, (int)128>"
+        return name.replace("(int)", "").replace("tr::", "").replace(" ", "")
+    wants = [want.replace(" ", "")]
+    for pipe, st in PIPE_STRUCT.items():
+        if st in want:
+            wants.append(wants[0].replace("k_raster<" + st, "k_raster<%d" % LEGACY_ID[pipe]))
+            wants.append(wants[0].replace("k_vertex_setup<" + st, "k_vertex_setup<%d" % (1 if pipe == "light_depth" else 0)))
     table, src = ncu_summaries()
-    for k, v in table.items():
-        if isinstance(v, dict) and want.replace(" ", "") in norm(k):
-            return dict(v, source=src)
+    for w in wants:
+        for k, v in table.items():
+            if isinstance(v, dict) and w in norm(k):
+                return dict(v, source=src)
     return None
 
 
-def issue_roofline(kernels, us, n_sm, sm_mhz):
+def issue_roofline(kernels, us, n_sm, sm_mhz, optional=()):
     """The bound these kernels actually run against: one warp instruction per cycle per SM sub-partition, which for
     FP32 work is also the FP32 pipe's rate (tools/probe/ffma2_probe.cu).  Warp instructions per launch come from the
     committed ncu capture of the named kernels (they do not depend on timing), `us` is measured live."""
     entries = [ncu_kernel_summary(k) for k in kernels]
     if any(e is None or "warp_instructions" not in e for e in entries) or not sm_mhz:
         return None
+    extra = [(k, ncu_kernel_summary(k)) for k in optional]          # counted when the committed capture has them
+    kernels = list(kernels) + [k for k, e in extra if e]
+    entries += [e for _, e in extra if e]
     instr = sum(e["warp_instructions"] for e in entries)
     peak = n_sm * 4 * sm_mhz * 1e6
     ach = instr / (us * 1e-6)
@@ -481,7 +505,7 @@ def run_ao(args, rank, world, dev, model, dist, tstream, sm_mhz=None):
     peak, _ = load_peaks()
     us_per_pass = ms * 1e3 / max(1, hi - lo)
     n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
-    issue = issue_roofline(["k_raster<-2,128>", "k_ao_accumulate", "k_vertex_setup<1>"], us_per_pass, n_sm, sm_mhz) if rank == 0 else None
+    issue = issue_roofline([raster_kernel("light_depth", 128), "k_ao_accumulate"], us_per_pass, n_sm, sm_mhz, optional=[setup_kernel("light_depth")]) if rank == 0 else None
     return {"metric": "AO depth passes/s", "value": AO_LIGHTS / (ms * 1e-3), "unit": "passes/s", "n_gpus": world,
             "scaling": "strong", "lights": AO_LIGHTS, "lights_per_gpu": hi - lo, "ms": ms,
             "exchange": ("none" if world == 1 else "k_ao_reduce_peers (own kernel, NVLink peer memory)" if use_peer else "NCCL all-reduce (faster than the own kernel in this run)"),
@@ -803,11 +827,11 @@ def run_gpu(args, rank, world, local_rank):
         def kernel_fig(p, shape):
             us = per[p][shape].get("K3_raster_visibility", 0.0)
             nb = ab[p]["K3_raster_visibility"]
-            e = ncu_kernel_summary("k_raster<%d,%s>" % (PIPE_ID[p], shape))
+            e = ncu_kernel_summary(raster_kernel(p, shape))
             return {"kernel": "k_raster<%s,%s>" % (p, shape), "cta_threads": int(shape), "us_per_launch": us, "algorithmic_bytes_per_launch": nb,
                     "achieved": nb / (us * 1e-6) / 1e9 if us else None, "frac": nb / (us * 1e-6) / 1e9 / peak if us else None,
                     "traffic": e["dram_bytes_per_launch"] if e else None,
-                    "issue": issue_roofline(["k_raster<%d,%s>" % (PIPE_ID[p], shape)], us, n_sm, sm_mhz) if us else None}
+                    "issue": issue_roofline([raster_kernel(p, shape)], us, n_sm, sm_mhz) if us else None}
 
         def frame_fig(p, shape):
             us = sum(per[p][shape].get(k, 0.0) for k in ("K1_vertex_setup", "K3_raster_visibility"))
@@ -832,7 +856,7 @@ def run_gpu(args, rank, world, local_rank):
             "batch": {"algorithmic_bytes_per_frame": batch_bytes, "us_per_frame": us_frame, "achieved": batch_bytes / (us_frame * 1e-6) / 1e9,
                       "frac": batch_bytes / (us_frame * 1e-6) / 1e9 / peak,
                       "note": "the timed region: both pipelines' frames overlapped, 128-thread shape",
-                      "issue": issue_roofline(["k_raster<1,128>", "k_raster<4,128>", "k_vertex_setup<0>", "k_vertex_setup<0>"],
+                      "issue": issue_roofline([raster_kernel("phong", 128), raster_kernel("darboux", 128), setup_kernel("phong"), setup_kernel("darboux")],
                                               2 * us_frame, n_sm, sm_mhz)}}
         if world == 1 and not QUICK:
             # what a rasteriser resolving visibility with global 64-bit atomicMin could reach on this box

@@ -156,11 +156,12 @@ def test_bench_finds_the_committed_ncu_summaries():
     spec = importlib.util.spec_from_file_location("bench_under_test", os.path.join(ROOT, "bench.py"))
     bench = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(bench)
-    for want in ("k_raster<1,256>", "k_raster<4,256>", "k_raster<1,128>", "k_raster<4,128>", "k_raster<-2,128>",
-                 "k_ao_accumulate", "k_vertex_setup<0>"):
+    rk, sk = bench.raster_kernel, bench.setup_kernel
+    for want in (rk("phong", 256), rk("darboux", 256), rk("phong", 128), rk("darboux", 128), rk("light_depth", 128),
+                 "k_ao_accumulate", sk("phong"), sk("darboux")):
         e = bench.ncu_kernel_summary(want)
         assert e is not None and e["warp_instructions"] > 0 and e["dram_bytes_per_launch"] > 0, want
-    assert bench.ncu_kernel_summary("k_raster<4,256>")["dram_bytes_per_launch"] > bench.ncu_kernel_summary("k_raster<1,256>")["dram_bytes_per_launch"] > 0
-    r = bench.issue_roofline(["k_raster<-2,128>", "k_ao_accumulate"], 56.6, 148, 1965.0)
+    assert bench.ncu_kernel_summary(rk("darboux", 256))["dram_bytes_per_launch"] > bench.ncu_kernel_summary(rk("phong", 256))["dram_bytes_per_launch"] > 0
+    r = bench.issue_roofline([rk("light_depth", 128), "k_ao_accumulate"], 56.6, 148, 1965.0)
     assert 0.5 < r["frac"] < 1.0 and abs(r["peak"] - 148 * 4 * 1.965) < 1e-6
     assert bench.issue_roofline(["no_such_kernel"], 10.0, 148, 1965.0) is None

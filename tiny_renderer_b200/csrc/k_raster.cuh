@@ -25,13 +25,13 @@
 #pragma once
 #include <type_traits>
 #include <cuda.h>               // CUtensorMap
-#include "k_shade.cuh"
+#include "pipeline.cuh"
 
 namespace tr {
 
 // Two CTA shapes of the same kernel (template parameter THREADS, measured in profiles/README.md):
-//   * 256 threads, 512-polygon lists, 6 CTAs per SM (40 registers, no spills; also the shared-memory limit; darboux,
-//     whose fragment code spills below 64 registers: 4) — a lone frame: the heavy tiles set the frame's duration, and
+//   * 256 threads, 512-polygon lists, 6 CTAs per SM (40 registers, no spills; also the shared-memory limit; pipelines
+//     with heavy_fragment set — darboux, whose fragment code spills below 64 registers: 4) — a lone frame: the heavy tiles set the frame's duration, and
 //     eight warps finish one sooner than four;
 //   * 128 threads, 192-polygon lists, 12 CTAs per SM (darboux: 8) — overlapped batches (view batches, the many-light
 //     AO batch): the same number of resident warps in smaller barrier groups, and a tile's ragged tail idles four
@@ -60,14 +60,13 @@ __host__ __device__ constexpr int raster_min_ctas(int threads, bool darboux) {
     return threads == kRasterThreads ? (darboux ? TR_MIN_CTAS_DARBOUX : TR_MIN_CTAS_LIGHT)
                                      : (darboux ? TR_MIN_CTAS_DARBOUX_BATCH : TR_MIN_CTAS_LIGHT_BATCH);
 }
-#define TR_RASTER_BOUNDS __launch_bounds__(THREADS, raster_min_ctas(THREADS, MODE == P_DARBOUX))
+#define TR_RASTER_BOUNDS __launch_bounds__(THREADS, raster_min_ctas(THREADS, PIPE::heavy_fragment))
 #ifndef TR_PIXELS_PER_LANE
 #define TR_PIXELS_PER_LANE 2
 #endif
 
-// Kernel modes: a pipeline id (P_DEFAULT..P_OCCLUSION) = visibility + shading of that pipeline.
-constexpr int kModeDepthOnly = -2;     // K4: shadow buffer, `>=` max, no culling upstream
-constexpr int kModeVisibility = -1;    // K3 alone: keys only (camera pass of the many-light AO batch)
+// Kernel modes: PIPE is a pipeline struct (pipelines/*.cuh: visibility + its `fragment` role) or one of the two tags of
+// pipeline.cuh, PassLightDepth (K4) / PassVisibility (K3 alone).
 
 struct RasterArgs {
     const float4* rec;
@@ -186,9 +185,10 @@ __device__ __noinline__ BlockState load_block_state(const unsigned long long* ke
     return st;
 }
 
-template <int MODE, int THREADS>
+template <class PIPE, int THREADS>
 __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u, const __grid_constant__ CUtensorMap rgb_map,
                                          const __grid_constant__ CUtensorMap rgb_map_top) {
+    constexpr int MODE = PIPE::id;
     constexpr bool DEPTH_ONLY = MODE == kModeDepthOnly;
     constexpr bool SHADE = MODE >= 0;
     constexpr int kRgbRow = kTileW * 3;
@@ -417,7 +417,9 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
                             fragment_depth(__float_as_int(r0.x), __float_as_int(r0.y), __float_as_int(r0.z), __float_as_int(r0.w),
                                            __float_as_int(r1.x), __float_as_int(r1.y), r1.z, r1.w, r2.x, px, qy, zz, v0, v1, v2);
                         }
-                        out = shade_pixel<SHADE ? MODE : 0>(sa, u, lo & kTriMask, px, qy, z, v0, v1, v2);
+                        const uint32_t tri = lo & kTriMask;
+                        const float4* rec = sa.rec + (size_t)tri * 4;
+                        out = PIPE::fragment(sa, u, FragmentIn{tri, px, qy, z, v0, v1, v2, __ldg(rec + 2), __ldg(rec + 3), sa.var + (size_t)tri * 6});
                     }
                     if (rgb_bulk) {
                         if (qy <= ty1) {                // (rows of a partial top tile beyond the frame have no place in s_rgb)

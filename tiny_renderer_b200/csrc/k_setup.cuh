@@ -3,7 +3,7 @@
 // (/root/reference/src/scene/shader.rs:285-316, 349-384, 416-437, 475-496, 549-595, 671-692, 711-747,
 // 809-830, 849-870), their helpers (shader.rs:116-165) and the bounding box of scene.rs:232-239.
 #pragma once
-#include "k_tile.cuh"
+#include "pipeline.cuh"
 
 namespace tr {
 
@@ -18,17 +18,12 @@ struct SetupOut {
     Bins bins;        // K2: per-cell polygon lists for the raster kernel that follows
 };
 
-// it_m * (n, 0) -> must have w == 0 -> normalised   (shader.rs:300-303, 368-371)
-__device__ __forceinline__ f3 normal_to_camera(const Uniforms& u, f3 n, unsigned long long* diag) {
-    f4 t = xform(u.it_m, f4{n.x, n.y, n.z, 0.0f});
-    if (!(t.w == 0.0f)) atomicAdd(&diag[D_W_ZERO], 1ull);
-    return unit3(f3{t.x, t.y, t.z});
-}
-
-// LIGHT_PASS: shadow/occlusion pass 1 — no culling, transform by u.shadow, no varyings.
-template <bool LIGHT_PASS>
+// PIPE: the pipeline whose `vertex` role writes the varyings (pipeline.cuh); PassLightDepth = shadow/occlusion pass 1 —
+// no culling, transform by u.shadow, no varyings.
+template <class PIPE>
 __global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__ geom, SetupOut out, const Uniforms u,
-                                                     int pipeline, unsigned long long* diag) {
+                                                     unsigned long long* diag) {
+    constexpr bool LIGHT_PASS = PIPE::id == kModeDepthOnly;
     // The tile kernel behind this one is launched with programmatic stream serialization (tinyr.cu: launch_raster): let
     // it start now; it waits for this grid's completion before it touches anything written here.
     asm volatile("griddepcontrol.launch_dependents;");
@@ -116,42 +111,20 @@ __global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__
     rec[1] = make_float4(__int_as_float(rx[2]), __int_as_float(ry[2]), rz[0], rz[1]);
     rec[2] = make_float4(rz[2], __int_as_float(drawn ? kFlagDrawn : 0u), g[9], g[10]);
     rec[3] = make_float4(g[11], g[12], g[13], g[14]);
-    if (LIGHT_PASS || !drawn || out.var == nullptr) return;
-
-    float v[kVarWords];
+    if constexpr (!LIGHT_PASS) {
+        if (!drawn || out.var == nullptr || PIPE::varying_words == 0) return;
+        float v[kVarWords];
 #pragma unroll
-    for (int k = 0; k < kVarWords; ++k) v[k] = 0.0f;
-    f3 nrm[3] = {{g[15], g[16], g[17]}, {g[18], g[19], g[20]}, {g[21], g[22], g[23]}};
-    if (pipeline == P_DEFAULT) {
-        // shader.rs:297-305
-        float d = dot3(u.t_light, normal_to_camera(u, face_normal, diag));
-        v[0] = d; v[1] = d; v[2] = d;
-    } else if (pipeline == P_PHONG || pipeline == P_SHADOW) {
-        // shader.rs:362-373, 725-736
+        for (int k = 0; k < kVarWords; ++k) v[k] = 0.0f;
+        VertexIn in;
 #pragma unroll
-        for (int i = 0; i < 3; ++i) v[i] = dot3(u.t_light, normal_to_camera(u, nrm[i], diag));
-    } else if (pipeline == P_DARBOUX) {
-        // shader.rs:562-584; rows 0 and 1 of the fragment shader's local basis (shader.rs:612-623) are
-        // constant per polygon: unit(P*(-1,1,0)), unit(P*(-1,0,1)) with P = columns m*p_i.
-        f3 tp[3];
+        for (int i = 0; i < 3; ++i) { in.p[i] = p[i]; in.n[i] = f3{g[15 + 3 * i], g[16 + 3 * i], g[17 + 3 * i]}; }
+        in.face_normal = face_normal;
+        PIPE::vertex(u, in, v, diag);
+        float4* var = out.var + (size_t)t * 6;
 #pragma unroll
-        for (int i = 0; i < 3; ++i) {
-            bool ok;
-            tp[i] = dehomog(xform(u.m, f4{p[i].x, p[i].y, p[i].z, 1.0f}), ok);
-        }
-        mat3 P = {{tp[0].x, tp[1].x, tp[2].x, tp[0].y, tp[1].y, tp[2].y, tp[0].z, tp[1].z, tp[2].z}};
-        f3 r0 = unit3(xform(P, f3{-1.0f, 1.0f, 0.0f}));
-        f3 r1 = unit3(xform(P, f3{-1.0f, 0.0f, 1.0f}));
-        v[3] = r0.x; v[4] = r0.y; v[5] = r0.z; v[6] = r1.x; v[7] = r1.y; v[8] = r1.z;
-#pragma unroll
-        for (int i = 0; i < 3; ++i) {
-            f3 n = normal_to_camera(u, nrm[i], diag);
-            v[12 + 3 * i] = n.x; v[13 + 3 * i] = n.y; v[14 + 3 * i] = n.z;   // column i of vertex_t_normals
-        }
+        for (int k = 0; k < (PIPE::varying_words + 3) / 4; ++k) var[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
     }
-    float4* var = out.var + (size_t)t * 6;
-#pragma unroll
-    for (int k = 0; k < 6; ++k) var[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
 }
 
 }  // namespace tr

@@ -1,5 +1,7 @@
-// k_shade.cuh — K5 fragment stage of the seven pipelines (device functions, called from the fused tile kernel in
-// k_raster.cuh for the winner of every pixel) and K6 ambient-occlusion accumulation (deferred, many-light batch).
+// k_shade.cuh — what the fragment closures share (samplers, color_blend, shadow-buffer lookups, the occlusion sample
+// loop) and K6 ambient-occlusion accumulation (deferred, many-light batch).  The fragment closures themselves are the
+// `fragment` roles of the pipeline structs under pipelines/ (pipeline.cuh), called from the fused tile kernel in
+// k_raster.cuh for the winner of every pixel.
 //
 // Texels are point-sampled through texture objects (the texture path).  Replaces the fragment closures of
 // /root/reference/src/scene/shader.rs (:318-333 default, :386-401 phong, :439-459 normal_map, :498-534 specular,
@@ -171,98 +173,6 @@ __device__ __forceinline__ uint32_t occlusion_gray(const float* shadow, const Un
     };
     if (untested) samples(std::true_type{}); else samples(std::false_type{});
     return cast_u8(occ * 255.0f + (1.0f - occ) * 0.0f);
-}
-
-// Fragment math of one pipeline for one covered pixel; returns packed RGB.  z and (b0, b1, b2) are the depth and the
-// barycentric coordinates of the pixel in polygon `tri` as the reference computes them (scene.rs:178-196).
-template <int PIPE>
-__device__ __forceinline__ uint32_t shade_pixel(const ShadeArgs& a, const Uniforms& u, uint32_t tri, int px, int py,
-                                                float z, float b0, float b1, float b2) {
-    const float4* r = a.rec + (size_t)tri * 4;
-    float4 r2 = __ldg(r + 2), r3 = __ldg(r + 3);
-    // uv = vertex_uvs * bar (2x3 mat-vec, column order)
-    f2 uv{(r2.z * b0 + r2.w * b1) + r3.x * b2, (r3.y * b0 + r3.z * b1) + r3.w * b2};
-    const float4* v = a.var + (size_t)tri * 6;
-
-    if (PIPE == P_OCCLUSION) {
-        // shader.rs:882-947 with the per-pass constants hoisted into Uniforms by K0
-        DiagLocal dl;
-        bool ok;
-        f3 wp = dehomog(xform(u.i_vpmv, f4{(float)px, (float)py, z, 1.0f}), ok);
-        dl.w_zero += ok ? 0u : 1u;
-        uint32_t g = occlusion_gray(a.shadow, u, px, py, z, wp, dl);
-        dl.flush(a.diag);
-        return pack_rgb(g, g, g);
-    }
-
-    uchar4 c = fetch_texel(a.maps, 0, 0, uv, a.diag);
-    float diff;
-    if (PIPE == P_DEFAULT) {
-        diff = __ldg(&v[0]).x;                                                   // shader.rs:329
-    } else if (PIPE == P_PHONG || PIPE == P_SHADOW) {
-        float4 in = __ldg(&v[0]);
-        diff = (b0 * in.x + b1 * in.y) + b2 * in.z;                              // shader.rs:397, 784
-        if (PIPE == P_SHADOW) {
-            bool ok;
-            DiagLocal dl;
-            f3 s = dehomog_shared(xform(u.shadow_from_screen, f4{(float)px, (float)py, z, 1.0f}), ok);
-            dl.w_zero += ok ? 0u : 1u;
-            float sv = shadow_lookup(a.shadow, s, u.width, u.width * u.height, dl);
-            dl.flush(a.diag);
-            float coef = (s.z + 1.0f < sv) ? 0.3f : 1.0f;                         // shader.rs:776-780
-            diff = diff * coef;
-        }
-    } else if (PIPE == P_NORMAL_MAP || PIPE == P_SPECULAR) {
-        f3 nm = decode_normal(fetch_texel(a.maps, 1, 1, uv, a.diag));
-        f4 t = xform(u.it_m, f4{nm.x, nm.y, nm.z, 0.0f});
-        f3 n = unit3_shared(f3{t.x, t.y, t.z});                                        // shader.rs:451-454
-        diff = dot3(u.t_light, n);
-        if (PIPE == P_SPECULAR) {
-            f3 refl = unit3_shared((n * dot3(u.t_light, n)) * 2.0f - u.t_light);         // shader.rs:515-518
-            float e = (float)fetch_texel(a.maps, 3, 3, uv, a.diag).x;              // util.rs:82: raw 0..255
-            float spec = 0.6f * powf(fmaxf(refl.z, 0.0f), e);
-            float k = diff + spec;
-            return pack_rgb(cast_u8(fminf(k * (float)c.x, 255.0f)), cast_u8(fminf(k * (float)c.y, 255.0f)),
-                            cast_u8(fminf(k * (float)c.z, 255.0f)));               // shader.rs:526-530
-        }
-    } else {   // P_DARBOUX, shader.rs:608-651
-        f3 nt = decode_normal(fetch_texel(a.maps, 2, 1, uv, a.diag));             // util.rs:61-63: sized by normal_map
-        float4 v0 = __ldg(&v[0]), v1 = __ldg(&v[1]), v2 = __ldg(&v[2]), v3 = __ldg(&v[3]), v4 = __ldg(&v[4]), v5 = __ldg(&v[5]);
-        mat3 N = {{v3.x, v3.w, v4.z, v3.y, v4.x, v4.w, v3.z, v4.y, v5.x}};         // vertex_t_normals, columns n0 n1 n2
-        f3 local_z = xform(N, f3{b0, b1, b2});
-        f3 row2 = unit3_shared(local_z);
-        // A rows: (v0.w v1.x v1.y), (v1.z v1.w v2.x), row2 — inverse by minors, each entry divided by det
-        float m11 = v0.w, m12 = v1.x, m13 = v1.y, m21 = v1.z, m22 = v1.w, m23 = v2.x, m31 = row2.x, m32 = row2.y, m33 = row2.z;
-        float mi1 = m22 * m33 - m32 * m23, mi2 = m21 * m33 - m31 * m23, mi3 = m21 * m32 - m31 * m22;
-        float det = m11 * mi1 - m12 * mi2 + m13 * mi3;
-        if (det == 0.0f) { atomicAdd(&a.diag[D_SINGULAR_BASIS], 1ull); return 0u; }
-        // every entry of the adjugate divided by det (nalgebra 3x3 try_inverse), one shared divisor
-        const float c12 = m13 * m32 - m33 * m12, c22 = m11 * m33 - m31 * m13, c32 = m12 * m31 - m32 * m11;
-        // uvs: r2.z r2.w r3.x = u0 u1 u2 ; r3.y r3.z r3.w = v0 v1 v2
-        const f3 du{r2.w - r2.z, r3.x - r2.z, 0.0f}, dv{r3.z - r3.y, r3.w - r3.y, 0.0f};
-        f3 lx, ly;
-        if (in_fast_division_range(det)) {
-            // The third column of the inverse only ever meets the zero component of du / dv.  On this branch det is
-            // finite and normal, hence so are the cofactors (products of unit-vector components): 0 * I(.,2) is a zero
-            // whose only possible trace is the sign of a zero sum, which no later step can turn into a different
-            // colour (it reaches the result through x / len, products and sums only).  So the column is not formed.
-            const SharedDivisor d = shared_divisor(det);
-            const float i00 = quotient(mi1, d), i01 = quotient(c12, d), i10 = quotient(-mi2, d), i11 = quotient(c22, d),
-                        i20 = quotient(mi3, d), i21 = quotient(c32, d);
-            lx = unit3_shared(f3{i01 * du.y + i00 * du.x, i11 * du.y + i10 * du.x, i21 * du.y + i20 * du.x});
-            ly = unit3_shared(f3{i01 * dv.y + i00 * dv.x, i11 * dv.y + i10 * dv.x, i21 * dv.y + i20 * dv.x});
-        } else {
-            const float c13 = m12 * m23 - m22 * m13, c23 = m13 * m21 - m23 * m11, c33 = m11 * m22 - m21 * m12;
-            const mat3 I = {{mi1 / det, c12 / det, c13 / det, -mi2 / det, c22 / det, c23 / det, mi3 / det, c32 / det, c33 / det}};
-            lx = unit3_shared(xform(I, du));
-            ly = unit3_shared(xform(I, dv));
-        }
-        f3 lz = unit3_shared(local_z);
-        mat3 B = {{lx.x, ly.x, lz.x, lx.y, ly.y, lz.y, lx.z, ly.z, lz.z}};
-        f3 n = unit3_shared(xform(B, nt));
-        diff = dot3(u.t_light, n);
-    }
-    return pack_rgb(blend_black(c.x, diff), blend_black(c.y, diff), blend_black(c.z, diff));
 }
 
 // K6 — many-light ambient occlusion (BASELINE config 4).  The camera's visibility does not depend on the light, so

@@ -4,10 +4,9 @@
 // There is no CPU fallback: every entry point fails with TR_ERR_NO_DEVICE / TR_ERR_CUDA without a GPU.
 #include "../../include/tinyr.h"
 #include "tr_error.h"
-#include "tr_prepare.h"
+#include "pipeline_table.cuh"
 #include "k_setup.cuh"
 #include "k_raster.cuh"
-#include "k_shade.cuh"
 #include "k_misc.cuh"
 #include "k_peer.cuh"
 #include "k_host.cuh"
@@ -40,7 +39,7 @@ struct tr_scene {
     int device = 0;
     uint32_t width = 0, height = 0, n_tri = 0, ring = 1, cur = 0;
     size_t n_px = 0;
-    int pipeline = P_DEFAULT;
+    int pipeline = kPipeDefault;
     // reference Scene state (scene.rs:32-35, defaults :66-69)
     f3 light{0.0f, 0.0f, -1.0f}, from{0.0f, 0.0f, 1.0f}, at{0.0f, 0.0f, 0.0f}, up{0.0f, 1.0f, 0.0f};
     Uniforms uni{};            // last camera-pass uniforms (for tr_scene_get_uniforms)
@@ -103,16 +102,40 @@ namespace {
 
 inline tr_scene::Slot& S(tr_scene* s) { return s->slots[s->cur]; }
 
+// ---- the pipeline registry (ShaderPipeline::new, shader.rs:97-112), generated from TR_PIPELINES ------------------
+// One entry per pipeline struct: its names, whether a light-depth pass runs first, its host `prepare` role and the
+// launchers of the kernels instantiated with its `vertex` / `fragment` roles.
+struct PipelineEntry {
+    const char* name;
+    const char* alias;
+    bool light_pass;
+    int (*prepare)(Uniforms&, uint32_t, uint32_t, f3, f3, f3, f3);
+    void (*setup)(tr_scene*, dim3, const SetupOut&, const Uniforms&);
+    void (*raster[2])(tr_scene*, dim3, const RasterArgs&, const ShadeArgs&, const Uniforms&);      // [0] lone-frame CTA shape, [1] batch shape
+};
+template <class PIPE> void launch_setup(tr_scene* s, dim3 grid, const SetupOut& out, const Uniforms& u);
+template <class PIPE, int T> void launch_raster(tr_scene* s, dim3 grid, const RasterArgs& a, const ShadeArgs& sa, const Uniforms& u);
+template <class PIPE> constexpr PipelineEntry pipeline_entry() {
+    return {PIPE::name, PIPE::alias, PIPE::light_pass, &PIPE::prepare, &launch_setup<PIPE>,
+            {&launch_raster<PIPE, kRasterThreads>, &launch_raster<PIPE, kRasterThreadsBatch>}};
+}
+const PipelineEntry kPipelines[kPipeCount] = {
+#define TR_X(N) pipeline_entry<Pipeline##N>(),
+    TR_PIPELINES(TR_X)
+#undef TR_X
+};
+// the two kernel modes that are not pipelines (pipeline.cuh)
+void (*const kRasterLightDepth[2])(tr_scene*, dim3, const RasterArgs&, const ShadeArgs&, const Uniforms&) =
+    {&launch_raster<PassLightDepth, kRasterThreads>, &launch_raster<PassLightDepth, kRasterThreadsBatch>};
+void (*const kRasterVisibility[2])(tr_scene*, dim3, const RasterArgs&, const ShadeArgs&, const Uniforms&) =
+    {&launch_raster<PassVisibility, kRasterThreads>, &launch_raster<PassVisibility, kRasterThreadsBatch>};
+
 int pipeline_from_name(const char* name) {
     if (!name) return -1;
-    static const struct { const char* n; int p; } table[] = {
-        {"default", P_DEFAULT}, {"phong", P_PHONG}, {"normal_map", P_NORMAL_MAP}, {"true_normal", P_NORMAL_MAP},
-        {"specular", P_SPECULAR}, {"darboux", P_DARBOUX}, {"shadow", P_SHADOW}, {"occlusion", P_OCCLUSION}};
-    for (auto& e : table) if (strcmp(e.n, name) == 0) return e.p;
+    for (int p = 0; p < kPipeCount; ++p)
+        if (strcmp(kPipelines[p].name, name) == 0 || (kPipelines[p].alias && strcmp(kPipelines[p].alias, name) == 0)) return p;
     return -1;
 }
-
-bool two_pass(int p) { return p == P_SHADOW || p == P_OCCLUSION; }
 
 int ensure_scratch(tr_scene* s, size_t bytes) {
     if (s->scratch_bytes >= bytes) return TR_OK;
@@ -398,8 +421,8 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     S(s).bins.parity ^= 1u;                 // this pass fills the other counter set; the kernel zeroes the one just used
     S(s).cam.bins = S(s).bins;
     S(s).lit.bins = S(s).bins;
-    if (light_pass) k_vertex_setup<true><<<grid, 128, 0, s->stream>>>(s->geom, S(s).lit, u, s->pipeline, s->diag);
-    else k_vertex_setup<false><<<grid, 128, 0, s->stream>>>(s->geom, S(s).cam, u, s->pipeline, s->diag);
+    if (light_pass) launch_setup<PassLightDepth>(s, grid, S(s).lit, u);
+    else kPipelines[s->pipeline].setup(s, grid, S(s).cam, u);
     return launch_ok("k_vertex_setup");
 }
 
@@ -418,10 +441,10 @@ ShadeArgs shade_args(tr_scene* s, bool fresh_rgb) {
 // for its completion and memory flush.  For a lone frame this hides the tile kernel's launch latency behind K1.
 // TINYR_NO_PDL=1 in the environment restores plain launches (A/B in profiles/README.md).
 static const bool g_pdl = getenv("TINYR_NO_PDL") == nullptr;
-template <int M, int T>
-static void launch_raster(tr_scene* s, dim3 grid, const RasterArgs& a, const ShadeArgs& sa, const Uniforms& u) {
+template <class PIPE, int T>
+void launch_raster(tr_scene* s, dim3 grid, const RasterArgs& a, const ShadeArgs& sa, const Uniforms& u) {
     if (!g_pdl) {
-        k_raster<M, T><<<grid, T, 0, s->stream>>>(a, sa, u, S(s).rgb_map, S(s).rgb_map_top);
+        k_raster<PIPE, T><<<grid, T, 0, s->stream>>>(a, sa, u, S(s).rgb_map, S(s).rgb_map_top);
         return;
     }
     cudaLaunchConfig_t cfg{};
@@ -430,7 +453,11 @@ static void launch_raster(tr_scene* s, dim3 grid, const RasterArgs& a, const Sha
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    cudaLaunchKernelEx(&cfg, k_raster<M, T>, a, sa, u, S(s).rgb_map, S(s).rgb_map_top);
+    cudaLaunchKernelEx(&cfg, k_raster<PIPE, T>, a, sa, u, S(s).rgb_map, S(s).rgb_map_top);
+}
+template <class PIPE>
+void launch_setup(tr_scene* s, dim3 grid, const SetupOut& out, const Uniforms& u) {
+    k_vertex_setup<PIPE><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->diag);
 }
 
 // mode: kModeDepthOnly (K4), kModeVisibility (K3 alone) or a pipeline id (K3 + K5 fused).
@@ -450,21 +477,10 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     dim3 grid(s->tiles_x * s->tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
     // CTA shape: 256 threads for a lone frame, 128 for overlapped batches (k_raster.cuh)
-    const bool batch_shape = s->overlapping || (s->debug_flags & 2u) != 0u;      // (debug bit 1: time the batch shape on a lone frame)
-#define TR_RASTER(M) do { if (batch_shape) launch_raster<M, kRasterThreadsBatch>(s, grid, a, sa, u); \
-                          else launch_raster<M, kRasterThreads>(s, grid, a, sa, u); } while (0)
-    switch (mode) {
-        case kModeDepthOnly: TR_RASTER(kModeDepthOnly); break;
-        case kModeVisibility: TR_RASTER(kModeVisibility); break;
-        case P_DEFAULT: TR_RASTER(P_DEFAULT); break;
-        case P_PHONG: TR_RASTER(P_PHONG); break;
-        case P_NORMAL_MAP: TR_RASTER(P_NORMAL_MAP); break;
-        case P_SPECULAR: TR_RASTER(P_SPECULAR); break;
-        case P_DARBOUX: TR_RASTER(P_DARBOUX); break;
-        case P_SHADOW: TR_RASTER(P_SHADOW); break;
-        default: TR_RASTER(P_OCCLUSION); break;
-    }
-#undef TR_RASTER
+    const int shape = (s->overlapping || (s->debug_flags & 2u) != 0u) ? 1 : 0;      // (debug bit 1: time the batch shape on a lone frame)
+    if (mode == kModeDepthOnly) kRasterLightDepth[shape](s, grid, a, sa, u);
+    else if (mode == kModeVisibility) kRasterVisibility[shape](s, grid, a, sa, u);
+    else kPipelines[mode].raster[shape](s, grid, a, sa, u);
     if (!depth_only && mode != kModeVisibility) s->kernel_launches[KS_SHADE]++;     // K5 runs inside this launch
     return launch_ok("k_raster");
 }
@@ -506,16 +522,16 @@ int render_impl(tr_scene* s) {
     int rc;
     Uniforms u{};
     u.n_triangles = s->n_tri; u.epoch = s->epoch;
-    if (two_pass(s->pipeline)) {
+    // every pass = its prepare role, all polygons through its vertex role, raster + its fragment role (scene.rs:200-266)
+    const PipelineEntry& pipe = kPipelines[s->pipeline];
+    if (pipe.light_pass) {
         if ((rc = prep_error(prepare_light(u, s->width, s->height, s->light, s->at, s->up)))) return rc;
         u.n_triangles = s->n_tri; u.epoch = s->epoch;
         if ((rc = run_setup(s, u, true))) return rc;
         if ((rc = run_raster(s, kModeDepthOnly, s->epoch, s->fresh_shadow, u, false))) return rc;
         s->fresh_shadow = false;
-        if ((rc = prep_error(prepare_camera_with_shadow(u, s->width, s->height, s->light, s->from, s->at, s->up, s->pipeline == P_OCCLUSION)))) return rc;
-    } else {
-        if ((rc = prep_error(prepare_camera(u, s->width, s->height, s->light, s->from, s->at, s->up)))) return rc;
     }
+    if ((rc = prep_error(pipe.prepare(u, s->width, s->height, s->light, s->from, s->at, s->up)))) return rc;
     u.debug_flags = s->debug_flags;
     if ((rc = run_setup(s, u, false))) return rc;
     if ((rc = run_raster(s, s->pipeline, s->epoch, s->fresh_keys, u, s->fresh_rgb))) return rc;

@@ -4,8 +4,7 @@
 
 namespace tr {
 
-// shader.rs:100-107 (+ README's `true_normal` spelling as an alias of normal_map).
-enum Pipeline : int { P_DEFAULT = 0, P_PHONG, P_NORMAL_MAP, P_SPECULAR, P_DARBOUX, P_SHADOW, P_OCCLUSION, P_COUNT };
+// (the pipeline ids are generated from the pipeline list: pipeline_table.cuh)
 
 enum DiagSlot : int {
     D_SHADOW_OOB = 0,   // shadow index >= w*h           (reference: index panic)
