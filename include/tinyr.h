@@ -37,7 +37,7 @@ typedef enum tr_status {
     TR_ERR_CUDA = -6,
     TR_ERR_NO_DEVICE = -7,            /* no CUDA device: there is NO CPU fallback */
     TR_ERR_REFERENCE_UNDEFINED = -8,  /* inputs for which the reference panics (singular basis, light = -z in occlusion, ...) */
-    TR_ERR_NCCL = -9,
+    TR_ERR_RESERVED_9 = -9,           /* (was TR_ERR_NCCL: the library links no NCCL; the sum over GPUs is its own peer-memory kernel) */
     TR_ERR_UNSUPPORTED = -10
 } tr_status;
 
@@ -133,6 +133,27 @@ int tr_scene_ao_ipc_handle(tr_scene* s, void* handle64);
 int tr_scene_ao_open_peers(tr_scene* s, const void* handles, uint32_t world, uint32_t rank);
 int tr_scene_ao_reduce_peers(tr_scene* s);
 int tr_scene_ao_close_peers(tr_scene* s);
+/* ---- native multi-GPU driver: one host process, one scene per device (tinyr_multi.inc) -------------------------------
+ * The reference's process entry (main.rs:12-36) drives one Scene; these drive the two batch modes that shard naturally
+ * over the devices of one box without Python, torch.distributed or NCCL.  `devices` lists CUDA ordinals (a device may
+ * appear twice: two scenes on one GPU, which lets a single-GPU box exercise the sharded paths).
+ *   tr_multi_render_views  device i renders views [i n / G, (i + 1) n / G); checksums / frames (optional, host, n entries
+ *                          in VIEW order) are written by the devices directly; no data-path exchange
+ *   tr_multi_render_ao     occlusion pipeline: device i accumulates lights [i n / G, (i + 1) n / G), then the accumulators
+ *                          are summed over the devices by k_ao_reduce_peers over NVLink peer memory (cudaDeviceEnablePeerAccess);
+ *                          accum_host (optional, w*h u32) receives the total; bit-identical for any G
+ *   tr_multi_set_camera    the same camera on every device's scene (lights / views are per call)
+ *   tr_multi_scene         the i-th device's scene, for everything else (getters, diagnostics, replicas of single frames) */
+typedef struct tr_multi tr_multi;
+int tr_multi_create(tr_multi** out, const tr_scene_desc* desc, const int32_t* devices, uint32_t n_devices);     /* desc->device is ignored */
+int tr_multi_create_from_dir(tr_multi** out, const char* asset_dir, const char* pipeline_name, uint32_t width, uint32_t height,
+                             const int32_t* devices, uint32_t n_devices, uint32_t ring);
+void tr_multi_destroy(tr_multi* m);
+uint32_t tr_multi_device_count(const tr_multi* m);
+tr_scene* tr_multi_scene(tr_multi* m, uint32_t i);
+int tr_multi_set_camera(tr_multi* m, const float look_from[3], const float look_at[3], const float up[3]);
+int tr_multi_render_views(tr_multi* m, const tr_view* views, uint32_t n_views, uint64_t* checksums, uint8_t* frames_rgb8_topdown);
+int tr_multi_render_ao(tr_multi* m, const float* light_dirs_xyz, uint32_t n_lights, uint32_t* accum_host);
 uint64_t tr_checksum_rgb8(const uint8_t* rgb8, size_t n_bytes);                  /* host twin of the device checksum */
 /* Deterministic light set for tr_scene_render_ao (host only): SplitMix64(seed) -> uniform sphere directions, computed
  * in double and rounded to f32, rejecting directions on which the reference's occlusion pipeline panics or reads

@@ -89,3 +89,49 @@ def test_cli_scripted_replay(tinyr, tmp_path):
          "--out", single)
     assert np.array_equal(tinyr.load_tga(path), tinyr.load_tga(single))
     assert tinyr.load_tga(path).any()
+
+
+def test_cli_batch_modes_views_and_lights(tinyr, oracle, tmp_path):
+    """SURVEY.md §5 flags: --views N (config 5 shape) and --lights N --seed S (config 4 shape) at test size through the
+    command line and the native multi-GPU driver, on 1 GPU and — when the box has them — on 2; --dump-visibility."""
+    import torch
+    d = assets.asset_dir("diablo")
+    if d is None:
+        pytest.skip("reference assets not staged")
+    m = get_model("diablo")
+    w, h = 320, 240
+    gpus = [1] + ([2] if torch.cuda.device_count() >= 2 else [])
+    # config 4: the CLI's image is round(sum of gray frames / n) of the oracle's sum over the same seeded lights
+    lights, _ = tinyr.generate_ao_lights(m.positions, 6, seed=1234)
+    o = oracle.OracleScene(w, h, m, "occlusion")
+    lf, la, up, _ = assets.view_vectors(0.0, 0.0)
+    o.set_camera(lf, la, up)
+    acc = o.render_ao(lights)
+    want = ((acc.astype(np.uint64) * 2 + 6) // 12).astype(np.uint8)[::-1]
+    for g in gpus:
+        path, vis = tmp_path / ("ao%d.tga" % g), tmp_path / ("vis%d.bin" % g)
+        text = _run(tinyr, "-p", d, "-s", "occlusion", "--width", w, "--height", h, "--lights", 6, "--seed", 1234, "--gpus", g,
+                    "--out", path, "--dump-visibility", vis)
+        assert re.search(r"ao: 6 lights .* on %d device" % g, text), text
+        img = tinyr.load_tga(path)
+        assert np.array_equal(img[..., 0], want) and np.array_equal(img[..., 1], want)
+        assert np.array_equal(np.fromfile(vis, np.uint32).reshape(h, w), o.raw_visibility())
+    # config 5: per-view checksums equal the host twin's checksum of the oracle-exact frames (phong: bit-exact pipeline)
+    n = 5
+    sums = []
+    og = oracle.OracleScene(w, h, m, "phong")
+    for k in range(n):
+        a = np.float32(0.25) + np.float32(2.0) * np.float32(3.14159274101257324) * np.float32(k) / np.float32(n)
+        lf = np.array([np.sin(a), 0.0, np.cos(a)], np.float32)
+        light = np.array([np.sin(np.float32(0.7)), 0.0, np.cos(np.float32(0.7))], np.float32)
+        parity.drive(og, lf, np.zeros(3, np.float32), np.array([0, 1, 0], np.float32), light)
+        sums.append(tinyr.checksum_rgb8(og.get_frame_buffer()))
+    for g in gpus:
+        path = tmp_path / ("views%d.tga" % g)
+        text = _run(tinyr, "-p", d, "-s", "phong", "--width", w, "--height", h, "--views", n, "--camera-angle", 0.25, "--light-angle", 0.7,
+                    "--gpus", g, "--out", path)
+        got = [int(x) for x in re.findall(r"view \d+ checksum (\d+)", text)]
+        # sinf/cosf of the CLI (libm, f32) against numpy's f32 sin/cos: equal on this platform; a 1-ulp difference in a
+        # camera vector would show up as a different checksum for that view only
+        assert got == sums, (g, got, sums)
+        assert np.array_equal(tinyr.load_tga(path), og.get_frame_buffer())

@@ -68,3 +68,80 @@ def test_peer_reduction_with_one_rank_is_the_identity(tinyr):
         g.ao_open_peers([b"\0" * 64] * 17, 0)             # more ranks than the kernel's flag area holds
     g.ao_close_peers()
     g.close()
+
+
+# ---- the native driver (tr_multi_*): one process, one scene per device -------------------------------------------
+# On a single-GPU box the device list names GPU 0 several times: the same code path (one host thread and one scene per
+# entry, accumulators summed by k_ao_reduce_peers) runs with every "device" on one GPU.
+
+def _device_lists():
+    n = _gpu_count()
+    lists = [[0], [0, 0], [0, 0, 0]]
+    if n >= 2:
+        lists += [[0, 1]]
+    if n >= 4:
+        lists += [[0, 1, 2, 3]]
+    if n >= 8:
+        lists += [list(range(8))]
+    return lists
+
+
+@pytest.mark.gpu
+def test_native_multi_ao_equals_single_scene_and_oracle():
+    """tr_multi_render_ao: lights in contiguous blocks per device entry, accumulators summed over peer memory by the
+    library's kernel — equal, bit for bit, to one scene rendering all lights, for every device list, and to the oracle."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
+    import assets
+    import oracle_lib
+    import tiny_renderer_b200 as tr
+    from tiny_renderer_b200.scene import MultiScene, Scene
+    m = assets.get_model("diablo")
+    w, h = 640, 360
+    lights, _ = tr.generate_ao_lights(m.positions, 13)
+    lf, la, up, _ = assets.view_vectors(0.0, 0.0)
+    one = Scene(w, h, m, "occlusion", ring=2)
+    one.set_camera(lf, la, up)
+    want = one.render_ao(lights)
+    o = oracle_lib.OracleScene(w, h, m, "occlusion")
+    o.set_camera(lf, la, up)
+    assert np.array_equal(want, o.render_ao(lights))
+    for devices in _device_lists():
+        g = MultiScene(w, h, m, "occlusion", devices, ring=2)
+        assert g.device_count() == len(devices)
+        g.set_camera(lf, la, up)
+        for rep in range(2):            # the barrier flags of the exchange kernel carry over from call to call
+            got = g.render_ao(lights)
+            assert np.array_equal(got, want), (devices, rep, int((got != want).sum()))
+        for i in range(len(devices)):   # every device's accumulator holds the total
+            assert np.array_equal(g.scene(i).read_ao(), want), (devices, i)
+        g.close()
+    one.close()
+
+
+@pytest.mark.gpu
+def test_native_multi_views_equal_single_scene():
+    """tr_multi_render_views: contiguous blocks of views per device entry; checksums and frames land in view order."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import math
+    import numpy as np
+    import assets
+    import tiny_renderer_b200 as tr
+    from tiny_renderer_b200.scene import MultiScene, Scene
+    m = assets.get_model("african_head")
+    w, h, n = 512, 384, 11
+    views = np.zeros((n, 12), np.float32)
+    for k in range(n):
+        lf, la, up, l = assets.view_vectors(2 * math.pi * k / n, 0.7)
+        views[k, 0:3], views[k, 3:6], views[k, 6:9], views[k, 9:12] = lf, la, up, l
+    one = Scene(w, h, m, "specular", ring=3)
+    want_frames = np.zeros((n, h, w, 3), np.uint8)
+    want = one.render_views(views, want_checksums=True, frames_out=want_frames)
+    for devices in _device_lists():
+        g = MultiScene(w, h, m, "specular", devices, ring=3)
+        frames = tr.pinned_empty((n, h, w, 3), np.uint8)            # sparse delivery from several scenes into one block
+        got = g.render_views(views, want_checksums=True, frames_out=frames)
+        assert np.array_equal(got, want), devices
+        assert np.array_equal(frames, want_frames), devices
+        g.close()
+    one.close()

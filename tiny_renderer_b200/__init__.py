@@ -23,7 +23,7 @@ DIAG_SLOTS = ("shadow_index_oob", "shadow_x_wrap", "texel_oob", "nan_depth", "w_
 
 TR_ERRORS = {-1: "TR_ERR_INVALID_ARGUMENT", -2: "TR_ERR_UNKNOWN_PIPELINE", -3: "TR_ERR_BAD_POLYGON", -4: "TR_ERR_IO",
              -5: "TR_ERR_FORMAT", -6: "TR_ERR_CUDA", -7: "TR_ERR_NO_DEVICE", -8: "TR_ERR_REFERENCE_UNDEFINED",
-             -9: "TR_ERR_NCCL", -10: "TR_ERR_UNSUPPORTED"}
+             -9: "TR_ERR_RESERVED_9", -10: "TR_ERR_UNSUPPORTED"}
 
 
 class TinyrError(RuntimeError):
@@ -109,6 +109,10 @@ def lib():
             "tr_selftest_round_u32": [ctypes.c_int, ctypes.POINTER(ctypes.c_uint64)],
             "tr_bench_atomic_min": [ctypes.c_int, u32, u32, u32, u32, ctypes.POINTER(ctypes.c_double)],
             "tr_selftest_exact_quotient": [ctypes.c_int, ctypes.c_uint64, ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)],
+            "tr_multi_create": [ctypes.POINTER(vp), ctypes.POINTER(_SceneDesc), vp, u32],
+            "tr_multi_create_from_dir": [ctypes.POINTER(vp), ctypes.c_char_p, ctypes.c_char_p, u32, u32, vp, u32, u32],
+            "tr_multi_set_camera": [vp, vp, vp, vp], "tr_multi_render_views": [vp, vp, u32, vp, vp],
+            "tr_multi_render_ao": [vp, vp, u32, vp],
             "tr_host_invalidate": [vp, ctypes.c_size_t], "tr_scene_transfer_stats": [vp, vp, i32],
             "tr_ao_generate_lights": [vp, u32, vp, vp, ctypes.c_uint64, u32, ctypes.c_float, vp, ctypes.POINTER(ctypes.c_uint64)],
         }
@@ -117,6 +121,9 @@ def lib():
             fn.argtypes = argtypes
             fn.restype = ctypes.c_int
         L.tr_scene_destroy.argtypes = [vp]; L.tr_scene_destroy.restype = None
+        L.tr_multi_destroy.argtypes = [vp]; L.tr_multi_destroy.restype = None
+        L.tr_multi_device_count.argtypes = [vp]; L.tr_multi_device_count.restype = ctypes.c_uint32
+        L.tr_multi_scene.argtypes = [vp, u32]; L.tr_multi_scene.restype = vp
         L.tr_mesh_free.argtypes = [ctypes.POINTER(_Mesh)]; L.tr_mesh_free.restype = None
         L.tr_pixels_free.argtypes = [ctypes.POINTER(_Pixels)]; L.tr_pixels_free.restype = None
         L.tr_last_error.restype = ctypes.c_char_p

@@ -78,6 +78,7 @@ struct tr_scene {
     // K9 (k_peer.cuh): the accumulators of all ranks, mapped through CUDA IPC by tr_scene_ao_open_peers
     uint32_t* peer_buf[kMaxPeers] = {};
     uint32_t peer_world = 0, peer_rank = 0, peer_value = 1;
+    bool peer_ipc = true;              // peer_buf entries were opened from CUDA IPC handles (one process per GPU); false: plain peer pointers (tr_multi_*)
     int* peer_status = nullptr;        // mapped host word the kernel sets when a barrier times out
     AoList ao_list{};                  // covered pixels of the camera view (many-light AO batch), allocated on first use
     unsigned long long* diag = nullptr;
@@ -380,7 +381,7 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
 
 void close_peers(tr_scene* s) {
     for (uint32_t r = 0; r < s->peer_world; ++r)
-        if (r != s->peer_rank && s->peer_buf[r]) cudaIpcCloseMemHandle(s->peer_buf[r]);
+        if (s->peer_ipc && r != s->peer_rank && s->peer_buf[r]) cudaIpcCloseMemHandle(s->peer_buf[r]);
     for (auto& p : s->peer_buf) p = nullptr;
     s->peer_world = 0;
 }
@@ -745,3 +746,4 @@ int tr_scene_device_frame(tr_scene* s, void** p) {
 }  // extern "C"
 
 #include "tinyr_batch.inc"
+#include "tinyr_multi.inc"

@@ -116,6 +116,28 @@ def pinned_empty(shape, dtype):
     return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
 
 
+def _scene_desc(width, height, model, pipeline_name, device, ring):
+    """tr_scene_desc for a Model; returns (desc, arrays to keep alive across the call)."""
+    d = _SceneDesc()
+    d.width, d.height = width, height
+    keep = [np.ascontiguousarray(model.positions, np.float32), np.ascontiguousarray(model.uvs, np.float32),
+            np.ascontiguousarray(model.normals, np.float32), np.ascontiguousarray(model.tri_idx, np.uint32)]
+    p, t, n, idx = keep
+    d.positions, d.n_positions = p.ctypes.data, len(p)
+    d.uvs, d.n_uvs = t.ctypes.data, len(t)
+    d.normals, d.n_normals = n.ctypes.data, len(n)
+    d.tri_idx, d.n_triangles = idx.ctypes.data, len(idx)
+    for field, img in zip(("texture", "normal_map", "normal_map_tangent", "specular_map"), model.maps):
+        img = np.ascontiguousarray(img, np.uint8)
+        keep.append(img)
+        setattr(d, field, _Image(img.ctypes.data, img.shape[1], img.shape[0]))
+    name = pipeline_name.encode()
+    keep.append(name)
+    d.pipeline_name = name
+    d.device, d.ring = int(device), int(ring)
+    return d, keep
+
+
 class Scene:
     """Scene::new(width, height, obj, texture, normal_map, normal_map_tangent, specular_map, pipeline_name)
     (scene.rs:47-56) with the model flattened into a `Model`."""
@@ -123,21 +145,7 @@ class Scene:
     def __init__(self, width, height, model, pipeline_name, device=0, ring=1):
         self.width, self.height = int(width), int(height)
         self.pipeline_name = pipeline_name
-        d = _SceneDesc()
-        d.width, d.height = self.width, self.height
-        self._keep = [np.ascontiguousarray(model.positions, np.float32), np.ascontiguousarray(model.uvs, np.float32),
-                      np.ascontiguousarray(model.normals, np.float32), np.ascontiguousarray(model.tri_idx, np.uint32)]
-        p, t, n, idx = self._keep
-        d.positions, d.n_positions = p.ctypes.data, len(p)
-        d.uvs, d.n_uvs = t.ctypes.data, len(t)
-        d.normals, d.n_normals = n.ctypes.data, len(n)
-        d.tri_idx, d.n_triangles = idx.ctypes.data, len(idx)
-        for field, img in zip(("texture", "normal_map", "normal_map_tangent", "specular_map"), model.maps):
-            img = np.ascontiguousarray(img, np.uint8)
-            self._keep.append(img)
-            setattr(d, field, _Image(img.ctypes.data, img.shape[1], img.shape[0]))
-        d.pipeline_name = pipeline_name.encode()
-        d.device, d.ring = int(device), int(ring)
+        d, self._keep = _scene_desc(self.width, self.height, model, pipeline_name, device, ring)
         h = ctypes.c_void_p()
         self._h = None
         _check(lib().tr_scene_create(ctypes.byref(h), ctypes.byref(d)))
@@ -308,6 +316,63 @@ class Scene:
         n = np.zeros(8, np.uint64)
         _check(lib().tr_scene_kernel_times(self._h, ms.ctypes.data, n.ctypes.data))
         return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(KERNEL_SLOTS)}
+
+
+class _BorrowedScene(Scene):
+    """A scene owned by a MultiScene: closing (or collecting) the view does not destroy it."""
+
+    def close(self):
+        self._h = None
+
+    __del__ = close
+
+
+class MultiScene:
+    """Native multi-GPU driver (tr_multi_*, include/tinyr.h): one host process, one scene per device.  `devices` lists
+    CUDA ordinals; listing a device twice puts two scenes on it (a single-GPU box can exercise the sharded paths)."""
+
+    def __init__(self, width, height, model, pipeline_name, devices, ring=1):
+        self.width, self.height = int(width), int(height)
+        d, self._keep = _scene_desc(self.width, self.height, model, pipeline_name, 0, ring)
+        dev = np.ascontiguousarray(devices, np.int32)
+        h = ctypes.c_void_p()
+        self._h = None
+        _check(lib().tr_multi_create(ctypes.byref(h), ctypes.byref(d), dev.ctypes.data, len(dev)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().tr_multi_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def device_count(self):
+        return int(lib().tr_multi_device_count(self._h))
+
+    def scene(self, i):
+        """Borrowed view of the i-th device's scene (owned by the MultiScene)."""
+        s = _BorrowedScene.__new__(_BorrowedScene)
+        s.width, s.height, s.pipeline_name, s._keep = self.width, self.height, None, []
+        s._h = ctypes.c_void_p(lib().tr_multi_scene(self._h, i))
+        return s
+
+    def set_camera(self, look_from, look_at, up):
+        a, b, c = _f3(look_from), _f3(look_at), _f3(up)
+        _check(lib().tr_multi_set_camera(self._h, a.ctypes.data, b.ctypes.data, c.ctypes.data))
+
+    def render_views(self, views, want_checksums=True, frames_out=None):
+        v = np.ascontiguousarray(views, np.float32).reshape(-1, 12)
+        cs = np.zeros(len(v), np.uint64) if want_checksums else None
+        _check(lib().tr_multi_render_views(self._h, v.ctypes.data, len(v), cs.ctypes.data if cs is not None else None,
+                                           frames_out.ctypes.data if frames_out is not None else None))
+        return cs
+
+    def render_ao(self, light_dirs):
+        lights = np.ascontiguousarray(light_dirs, np.float32).reshape(-1, 3)
+        out = np.empty((self.height, self.width), np.uint32)
+        _check(lib().tr_multi_render_ao(self._h, lights.ctypes.data, len(lights), out.ctypes.data))
+        return out
 
 
 def make_views(look_from, look_at, up, light):
