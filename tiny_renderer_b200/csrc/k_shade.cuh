@@ -221,21 +221,22 @@ __global__ void __launch_bounds__(kShadeThreads) k_ao_compact(const ShadeArgs a,
 }
 
 #ifndef TR_AO_MIN_CTAS
-#define TR_AO_MIN_CTAS 5      // 48 registers: the grid-stride form spills at 40 (6 CTAs); r1 measured 5 and 6 CTAs equal (tools/tune_ao.sh)
+#define TR_AO_MIN_CTAS 6      // 40 registers; measured best with groups of 8 (tools/tune_ao.sh)
 #endif
-constexpr int kAoGridCtas = 148 * TR_AO_MIN_CTAS;        // one resident wave
-__global__ void __launch_bounds__(kShadeThreads, TR_AO_MIN_CTAS) k_ao_accumulate(const ShadeArgs a, const Uniforms u, const AoList in) {
-    const uint32_t n = *in.count;
-    for (uint32_t i = blockIdx.x * kShadeThreads + threadIdx.x; i < n; i += gridDim.x * kShadeThreads) {
-        const float4 frag = __ldg(&in.frag[i]);
-        const uint32_t pix = __ldg(&in.pix[i]);
-        const int px = (int)(pix & 0xffffu), py = (int)(pix >> 16);
-        DiagLocal dl;
-        const uint32_t g = occlusion_gray(a.shadow, u, px, py, frag.w, f3{frag.x, frag.y, frag.z}, dl);
-        dl.flush(a.diag);
-        // integer add: the order of the light passes (which may overlap on the device) cannot change the sum
-        atomicAdd(&a.ao_accum[(size_t)py * u.width + px], g);
-    }
+// One thread per entry of the compacted list.  (A fixed grid walking the list with a stride — which needs no count on
+// the host — was measured in r2: it spills at 40 registers, and at 5 CTAs / 48 registers the kernel alone takes 58.1 us
+// against 49.6; the host now learns the count behind the first light passes' depth work instead, tinyr_batch.inc.)
+__global__ void __launch_bounds__(kShadeThreads, TR_AO_MIN_CTAS) k_ao_accumulate(const ShadeArgs a, const Uniforms u, const AoList in, uint32_t n) {
+    const uint32_t i = blockIdx.x * kShadeThreads + threadIdx.x;
+    if (i >= n) return;
+    const float4 frag = __ldg(&in.frag[i]);
+    const uint32_t pix = __ldg(&in.pix[i]);
+    const int px = (int)(pix & 0xffffu), py = (int)(pix >> 16);
+    DiagLocal dl;
+    const uint32_t g = occlusion_gray(a.shadow, u, px, py, frag.w, f3{frag.x, frag.y, frag.z}, dl);
+    dl.flush(a.diag);
+    // integer add: the order of the light passes (which may overlap on the device) cannot change the sum
+    atomicAdd(&a.ao_accum[(size_t)py * u.width + px], g);
 }
 
 }  // namespace tr

@@ -81,6 +81,8 @@ struct tr_scene {
     bool peer_ipc = true;              // peer_buf entries were opened from CUDA IPC handles (one process per GPU); false: plain peer pointers (tr_multi_*)
     int* peer_status = nullptr;        // mapped host word the kernel sets when a barrier times out
     AoList ao_list{};                  // covered pixels of the camera view (many-light AO batch), allocated on first use
+    uint32_t* ao_count_host = nullptr; // pinned: length of ao_list, copied behind k_ao_compact
+    cudaEvent_t ev_ao_count = nullptr;
     unsigned long long* diag = nullptr;
     // K10 (k_host.cuh): [0] bytes / [1] tile rows stored into host frames by the sparse delivery; host-side counters beside them
     unsigned long long* host_stats = nullptr;
@@ -392,6 +394,8 @@ void destroy_impl(tr_scene* s) {
     if (s->stream) cudaStreamSynchronize(s->stream);
     close_peers(s);
     if (s->peer_status) cudaFreeHost(s->peer_status);
+    if (s->ao_count_host) cudaFreeHost(s->ao_count_host);
+    if (s->ev_ao_count) cudaEventDestroy(s->ev_ao_count);
     for (auto& sp : s->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : s->event_pool) cudaEventDestroy(e);
     if (s->ev_begin) cudaEventDestroy(s->ev_begin);
@@ -488,12 +492,15 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
 
 // K6: deferred occlusion pass of the many-light AO batch.
 // K6 part 1: compact the covered pixels of the camera slot (depth + world position), once per AO batch.  The count
-// stays on the device: K6 part 2 reads it there, so the batch never waits for the host.
+// travels to the host asynchronously (mapped word + event): tr_scene_render_ao only waits for it after it has queued the
+// depth passes of the first lights, so the device never idles on the round trip.
 int run_ao_compact(tr_scene* s, const Uniforms& u) {
     if (!s->ao_list.frag) {
         CU(cudaMalloc(&s->ao_list.frag, s->n_px * sizeof(float4)));
         CU(cudaMalloc(&s->ao_list.pix, s->n_px * 4));
         CU(cudaMalloc(&s->ao_list.count, 4));
+        CU(cudaHostAlloc((void**)&s->ao_count_host, 4, cudaHostAllocDefault));
+        CU(cudaEventCreateWithFlags(&s->ev_ao_count, cudaEventDisableTiming));
     }
     CU(cudaMemsetAsync(s->ao_list.count, 0, 4, s->stream));
     ShadeArgs a = shade_args(s, false);
@@ -502,17 +509,20 @@ int run_ao_compact(tr_scene* s, const Uniforms& u) {
         Scoped sp(s, KS_AO);
         k_ao_compact<<<grid, kShadeThreads, 0, s->stream>>>(a, u, s->ao_list);
     }
-    return launch_ok("k_ao_compact");
+    int rc = launch_ok("k_ao_compact");
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(s->ao_count_host, s->ao_list.count, 4, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaEventRecord(s->ev_ao_count, s->stream));
+    return TR_OK;
 }
 
-// K6 part 2: one light's occlusion term for every covered pixel, added into the accumulator.  A fixed grid walks the
-// compacted list (grid-stride), whose length it reads from device memory.
-int run_ao_accumulate(tr_scene* s, const Uniforms& u) {
+// K6 part 2: one light's occlusion term for every covered pixel, added into the accumulator.
+int run_ao_accumulate(tr_scene* s, const Uniforms& u, uint32_t n_covered) {
+    if (n_covered == 0) return TR_OK;
     ShadeArgs a = shade_args(s, false);                  // shadow buffer of the current (light) slot
-    const size_t want = (s->n_px + kShadeThreads - 1) / kShadeThreads;
-    dim3 grid((unsigned)std::min<size_t>(want, (size_t)kAoGridCtas));
+    dim3 grid((n_covered + kShadeThreads - 1) / kShadeThreads);
     Scoped sp(s, KS_AO);
-    k_ao_accumulate<<<grid, kShadeThreads, 0, s->stream>>>(a, u, s->ao_list);
+    k_ao_accumulate<<<grid, kShadeThreads, 0, s->stream>>>(a, u, s->ao_list, n_covered);
     return launch_ok("k_ao_accumulate");
 }
 

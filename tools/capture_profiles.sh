@@ -26,10 +26,10 @@ ncu --metrics gpu__time_duration.sum --clock-control none -s 700 -c 900 --csv --
 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --cache-control none --clock-control none \
     --kernel-name-base demangled -k regex:"k_raster" -s 420 -c 256 --csv --log-file $out/${tag}_steady.csv \
     python bench.py --steps 2 --warmup 3 > $out/${tag}_ncu5.log 2>&1
-ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:"k_raster<.*128>|k_vertex_setup|k_frame_to_host" -s 40 -c 10 -f -o $out/${tag}_full \
+ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:"k_raster<.*128>|k_vertex_setup" -s 120 -c 16 -f -o $out/${tag}_full \
     python bench.py --steps 2 --warmup 3 > $out/${tag}_ncu2.log 2>&1
 # the 256-thread shape of the tile kernel only runs in the bench's one-frame-at-a-time sections
-ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:"k_raster<.*256>" -s 70 -c 4 -f -o $out/${tag}_full_lone \
+ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:"k_raster<.*256>" -s 78 -c 8 -f -o $out/${tag}_full_lone \
     python bench.py --steps 2 --warmup 3 > $out/${tag}_ncu4.log 2>&1
 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:"k_frame_to_host" -s 300 -c 3 -f -o $out/${tag}_full_host \
     python bench.py --steps 2 --warmup 3 > $out/${tag}_ncu6.log 2>&1
