@@ -445,3 +445,42 @@ def test_config4_render_ao_at_4k_matches_oracle(tinyr, oracle):
         d = g.diagnostics()
         assert d["shadow_index_oob"] == 0 and d["shadow_x_wrap"] == 0
         g.close()
+
+
+@pytest.mark.parametrize("pipeline,ring", [("default", 8), ("darboux", 4), ("shadow", 8), ("occlusion", 2), ("specular", 5)])
+def test_small_frames_several_views_per_launch(tinyr, oracle, pipeline, ring):
+    """at small resolutions (the reference's 800x800) a view batch runs several views per launch
+    (k_vertex_setup_views / k_raster_views: the view is a grid dimension).  Every view must equal the single-frame render
+    bit for bit — frames, checksums, and the state the scene is left in — for one- and two-pass pipelines, ragged last
+    chunks, and against the oracle."""
+    from tiny_renderer_b200.scene import Scene
+    m = get_model("african_head" if pipeline in ("default", "specular") else "diablo")
+    w, h = 800, 800
+    n = 11
+    views = turntable(n, light_angle=0.9)
+    g = Scene(w, h, m, pipeline, ring=ring)
+    frames = tinyr.pinned_empty((n, h, w, 3), np.uint8)
+    cs = g.render_views(views, want_checksums=True, frames_out=frames)
+    assert g.kernel_times()["K3_raster_visibility"][1] < n          # fewer tile-kernel launches than views
+    single = Scene(w, h, m, pipeline)
+    for k in range(n):
+        parity.drive(single, views[k, 0:3], views[k, 3:6], views[k, 6:9], views[k, 9:12])
+        f = single.get_frame_buffer()
+        assert np.array_equal(f, frames[k]), k
+        assert int(cs[k]) == tinyr.checksum_rgb8(f), k
+    # the scene is left on the last view, with all of its buffers
+    assert np.array_equal(g.get_frame_buffer(), frames[n - 1])
+    assert np.array_equal(g.raw_visibility(), single.raw_visibility())
+    assert np.array_equal(g.raw_z().view(np.uint32), single.raw_z().view(np.uint32))
+    if pipeline in ("shadow", "occlusion"):
+        assert np.array_equal(g.raw_shadow().view(np.uint32), single.raw_shadow().view(np.uint32))
+    # a second batch on the same scene (slots hold old frames), without host outputs, then a single frame on top
+    g.render_views(views[::-1], want_checksums=False)
+    assert np.array_equal(g.get_frame_buffer(), frames[0])
+    parity.drive(g, views[3, 0:3], views[3, 3:6], views[3, 6:9], views[3, 9:12])
+    assert np.array_equal(g.get_frame_buffer(), frames[3])
+    o = oracle.OracleScene(w, h, m, pipeline)
+    parity.drive(o, views[5, 0:3], views[5, 3:6], views[5, 6:9], views[5, 9:12])
+    d = np.abs(frames[5].astype(np.int16) - o.get_frame_buffer().astype(np.int16)).max(axis=2)
+    assert (d <= (1 if pipeline == "specular" else 0)).mean() >= 0.999
+    g.close(); single.close()

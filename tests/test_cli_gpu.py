@@ -120,10 +120,14 @@ def test_cli_batch_modes_views_and_lights(tinyr, oracle, tmp_path):
     n = 5
     sums = []
     og = oracle.OracleScene(w, h, m, "phong")
+    import ctypes
+    libm = ctypes.CDLL("libm.so.6")             # the CLI's sinf / cosf (numpy's float32 sin is its own SIMD routine)
+    for f in (libm.sinf, libm.cosf):
+        f.argtypes, f.restype = [ctypes.c_float], ctypes.c_float
     for k in range(n):
         a = np.float32(0.25) + np.float32(2.0) * np.float32(3.14159274101257324) * np.float32(k) / np.float32(n)
-        lf = np.array([np.sin(a), 0.0, np.cos(a)], np.float32)
-        light = np.array([np.sin(np.float32(0.7)), 0.0, np.cos(np.float32(0.7))], np.float32)
+        lf = np.array([libm.sinf(float(a)), 0.0, libm.cosf(float(a))], np.float32)
+        light = np.array([libm.sinf(0.7), 0.0, libm.cosf(0.7)], np.float32)
         parity.drive(og, lf, np.zeros(3, np.float32), np.array([0, 1, 0], np.float32), light)
         sums.append(tinyr.checksum_rgb8(og.get_frame_buffer()))
     for g in gpus:
@@ -131,7 +135,5 @@ def test_cli_batch_modes_views_and_lights(tinyr, oracle, tmp_path):
         text = _run(tinyr, "-p", d, "-s", "phong", "--width", w, "--height", h, "--views", n, "--camera-angle", 0.25, "--light-angle", 0.7,
                     "--gpus", g, "--out", path)
         got = [int(x) for x in re.findall(r"view \d+ checksum (\d+)", text)]
-        # sinf/cosf of the CLI (libm, f32) against numpy's f32 sin/cos: equal on this platform; a 1-ulp difference in a
-        # camera vector would show up as a different checksum for that view only
         assert got == sums, (g, got, sums)
         assert np.array_equal(tinyr.load_tga(path), og.get_frame_buffer())

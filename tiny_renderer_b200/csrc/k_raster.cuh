@@ -185,9 +185,11 @@ __device__ __noinline__ BlockState load_block_state(const unsigned long long* ke
     return st;
 }
 
+// The tile kernel's body: one CTA, one tile.  launch_pos selects the tile through a.tile_order; the tensor maps must
+// live in parameter (or constant / global) memory.
 template <class PIPE, int THREADS>
-__global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u, const __grid_constant__ CUtensorMap rgb_map,
-                                         const __grid_constant__ CUtensorMap rgb_map_top) {
+__device__ __forceinline__ void raster_tile(const RasterArgs& a, const ShadeArgs& sa, const Uniforms& u, const CUtensorMap* rgb_map,
+                                            const CUtensorMap* rgb_map_top, uint32_t launch_pos) {
     constexpr int MODE = PIPE::id;
     constexpr bool DEPTH_ONLY = MODE == kModeDepthOnly;
     constexpr bool SHADE = MODE >= 0;
@@ -206,7 +208,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // CTAs are handed out in launch order; for a lone frame tile_order lists the tiles from the screen centre outwards
     // so that the tiles that usually carry the geometry start first and the cheap border tiles fill the tail of the grid.
-    const uint32_t tile_xy = __ldg(&a.tile_order[blockIdx.x]);
+    const uint32_t tile_xy = __ldg(&a.tile_order[launch_pos]);
     const uint32_t tile = (tile_xy >> 16) * a.tiles_x + (tile_xy & 0xffffu);
     const int tx0 = (int)(tile_xy & 0xffffu) * kTileW, ty0 = (int)(tile_xy >> 16) * kTileH;
     const int tx1 = min(tx0 + kTileW, (int)a.width) - 1, ty1 = min(ty0 + kTileH, (int)a.height) - 1;
@@ -484,7 +486,7 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
                 // border) is done by the hardware.
                 const uint32_t src = (uint32_t)__cvta_generic_to_shared(s_rgb);
                 const int x = tx0 * 3, y = (int)a.height - ty0 - rows;
-                const uint64_t map = reinterpret_cast<uint64_t>(rows == kTileH ? &rgb_map : &rgb_map_top);
+                const uint64_t map = reinterpret_cast<uint64_t>(rows == kTileH ? rgb_map : rgb_map_top);
                 asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                              :: "l"(map), "r"(src), "r"(x), "r"(y) : "memory");
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -500,6 +502,32 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     } else if (SHADE && touched && tid == 0) {
         sa.rgb_zero[tile] = 0u;
     }
+}
+
+template <class PIPE, int THREADS>
+__global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u, const __grid_constant__ CUtensorMap rgb_map,
+                                         const __grid_constant__ CUtensorMap rgb_map_top) {
+    raster_tile<PIPE, THREADS>(a, sa, u, &rgb_map, &rgb_map_top, blockIdx.x);
+}
+
+// Several views in ONE launch (multi-view-per-launch batching at small resolutions): blockIdx.y
+// selects the view, i.e. one frame slot's buffers and one camera's uniforms out of the parameter block.  At 800x800 — the
+// reference's own resolution (main.rs:6-7) — a frame is 325 tiles for 148 SMs and two launches per frame leave the device
+// launch- and latency-bound; a batch of V views becomes two launches of V x 325 CTAs.  Every access to the arguments is
+// an indexed constant-bank load here instead of an immediate operand, which the 4K paths (k_raster above) do not pay.
+constexpr int kMaxViewsPerLaunch = 8;
+struct ViewArgs {
+    RasterArgs a;
+    ShadeArgs sa;
+    Uniforms u;
+    CUtensorMap rgb_map, rgb_map_top;
+};
+struct ViewBatch { ViewArgs v[kMaxViewsPerLaunch]; };
+static_assert(sizeof(ViewBatch) <= 32000, "kernel parameters are limited to 32,764 bytes");
+template <class PIPE, int THREADS>
+__global__ void TR_RASTER_BOUNDS k_raster_views(const __grid_constant__ ViewBatch b) {
+    const ViewArgs& v = b.v[blockIdx.y];
+    raster_tile<PIPE, THREADS>(v.a, v.sa, v.u, &v.rgb_map, &v.rgb_map_top, blockIdx.x);
 }
 
 }  // namespace tr

@@ -21,8 +21,7 @@ struct SetupOut {
 // PIPE: the pipeline whose `vertex` role writes the varyings (pipeline.cuh); PassLightDepth = shadow/occlusion pass 1 —
 // no culling, transform by u.shadow, no varyings.
 template <class PIPE>
-__global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__ geom, SetupOut out, const Uniforms u,
-                                                     unsigned long long* diag) {
+__device__ __forceinline__ void vertex_setup(const float4* __restrict__ geom, const SetupOut& out, const Uniforms& u, unsigned long long* diag) {
     constexpr bool LIGHT_PASS = PIPE::id == kModeDepthOnly;
     // The tile kernel behind this one is launched with programmatic stream serialization (tinyr.cu: launch_raster): let
     // it start now; it waits for this grid's completion before it touches anything written here.
@@ -125,6 +124,23 @@ __global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__
 #pragma unroll
         for (int k = 0; k < (PIPE::varying_words + 3) / 4; ++k) var[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
     }
+}
+
+template <class PIPE>
+__global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__ geom, const SetupOut out, const Uniforms u,
+                                                     unsigned long long* diag) {
+    vertex_setup<PIPE>(geom, out, u, diag);
+}
+
+// Several views in one launch (see k_raster_views): blockIdx.y selects the view's uniforms and frame slot.
+constexpr int kMaxSetupViews = 8;
+struct SetupViewArgs { SetupOut out; Uniforms u; };
+struct SetupViewBatch { SetupViewArgs v[kMaxSetupViews]; };
+template <class PIPE>
+__global__ void __launch_bounds__(128) k_vertex_setup_views(const float4* __restrict__ geom, const __grid_constant__ SetupViewBatch b,
+                                                           unsigned long long* diag) {
+    const SetupViewArgs& v = b.v[blockIdx.y];
+    vertex_setup<PIPE>(geom, v.out, v.u, diag);
 }
 
 }  // namespace tr

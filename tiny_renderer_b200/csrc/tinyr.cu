@@ -115,12 +115,17 @@ struct PipelineEntry {
     int (*prepare)(Uniforms&, uint32_t, uint32_t, f3, f3, f3, f3);
     void (*setup)(tr_scene*, dim3, const SetupOut&, const Uniforms&);
     void (*raster[2])(tr_scene*, dim3, const RasterArgs&, const ShadeArgs&, const Uniforms&);      // [0] lone-frame CTA shape, [1] batch shape
+    void (*setup_views)(tr_scene*, dim3, const SetupViewBatch&);                                   // several views per launch (small frames)
+    void (*raster_views)(tr_scene*, dim3, const ViewBatch&);
 };
 template <class PIPE> void launch_setup(tr_scene* s, dim3 grid, const SetupOut& out, const Uniforms& u);
 template <class PIPE, int T> void launch_raster(tr_scene* s, dim3 grid, const RasterArgs& a, const ShadeArgs& sa, const Uniforms& u);
+template <class PIPE> void launch_setup_views(tr_scene* s, dim3 grid, const SetupViewBatch& b);
+template <class PIPE> void launch_raster_views(tr_scene* s, dim3 grid, const ViewBatch& b);
 template <class PIPE> constexpr PipelineEntry pipeline_entry() {
     return {PIPE::name, PIPE::alias, PIPE::light_pass, &PIPE::prepare, &launch_setup<PIPE>,
-            {&launch_raster<PIPE, kRasterThreads>, &launch_raster<PIPE, kRasterThreadsBatch>}};
+            {&launch_raster<PIPE, kRasterThreads>, &launch_raster<PIPE, kRasterThreadsBatch>},
+            &launch_setup_views<PIPE>, &launch_raster_views<PIPE>};
 }
 const PipelineEntry kPipelines[kPipeCount] = {
 #define TR_X(N) pipeline_entry<Pipeline##N>(),
@@ -464,10 +469,28 @@ template <class PIPE>
 void launch_setup(tr_scene* s, dim3 grid, const SetupOut& out, const Uniforms& u) {
     k_vertex_setup<PIPE><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->diag);
 }
+template <class PIPE>
+void launch_setup_views(tr_scene* s, dim3 grid, const SetupViewBatch& b) {
+    k_vertex_setup_views<PIPE><<<grid, 128, 0, s->stream>>>(s->geom, b, s->diag);
+}
+template <class PIPE>
+void launch_raster_views(tr_scene* s, dim3 grid, const ViewBatch& b) {
+    constexpr int T = kRasterThreadsBatch;
+    if (!g_pdl) {
+        k_raster_views<PIPE, T><<<grid, T, 0, s->stream>>>(b);
+        return;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = dim3(T); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, k_raster_views<PIPE, T>, b);
+}
 
-// mode: kModeDepthOnly (K4), kModeVisibility (K3 alone) or a pipeline id (K3 + K5 fused).
-int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms& u, bool fresh_rgb) {
-    const bool depth_only = mode == kModeDepthOnly;
+// Arguments of the tile kernel for the current slot.
+RasterArgs raster_args(tr_scene* s, bool depth_only, uint32_t epoch, bool fresh, bool row_order) {
     RasterArgs a{};
     a.rec = depth_only ? S(s).lit.rec : S(s).cam.rec;
     a.bbox = depth_only ? S(s).lit.bbox : S(s).cam.bbox;
@@ -475,10 +498,59 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     a.n_triangles = s->n_tri; a.width = s->width; a.height = s->height; a.tiles_x = s->tiles_x;
     a.epoch = epoch; a.fresh = fresh ? 1 : 0;
     a.keys = S(s).keys; a.tile_state = S(s).tile_state; a.depth = S(s).shadow; a.depth_clear = S(s).shadow_clear; a.diag = s->diag;
+    a.tile_order = s->tile_order + (row_order ? (size_t)s->tiles_x * s->tiles_y : 0);
+    return a;
+}
+
+// Several cleared views in one launch per stage (k_raster_views / k_vertex_setup_views): view j renders into slot
+// slots[j] with uniforms cam[j] (and lit[j] for the light pass of the two-pass pipelines).  Everything on s->stream.
+int run_views_multi(tr_scene* s, const uint32_t* slots, const Uniforms* lit, const Uniforms* cam, uint32_t m) {
+    const PipelineEntry& pipe = kPipelines[s->pipeline];
+    const uint32_t keep = s->cur;
+    const dim3 sgrid((s->n_tri + 127) / 128, m), rgrid(s->tiles_x * s->tiles_y, m);
+    int rc = TR_OK;
+    for (int pass = pipe.light_pass ? 0 : 1; pass < 2 && rc == TR_OK; ++pass) {
+        const bool light = pass == 0;
+        static SetupViewBatch sb;           // (parameter blocks are copied by the launch; static: 10 KB off the stack)
+        static ViewBatch vb;
+        static std::mutex mu;
+        std::lock_guard<std::mutex> lock(mu);
+        for (uint32_t j = 0; j < m; ++j) {
+            s->cur = slots[j];
+            const Uniforms& u = light ? lit[j] : cam[j];
+            S(s).bins.parity ^= 1u;
+            S(s).cam.bins = S(s).bins;
+            S(s).lit.bins = S(s).bins;
+            sb.v[j].out = light ? S(s).lit : S(s).cam;
+            sb.v[j].u = u;
+            vb.v[j].a = raster_args(s, light, 0, true, true);
+            vb.v[j].sa = shade_args(s, true);
+            vb.v[j].u = u;
+            vb.v[j].rgb_map = S(s).rgb_map;
+            vb.v[j].rgb_map_top = S(s).rgb_map_top;
+        }
+        if (s->n_tri) {
+            s->kernel_launches[KS_SETUP]++;
+            if (light) launch_setup_views<PassLightDepth>(s, sgrid, sb);
+            else pipe.setup_views(s, sgrid, sb);
+            if ((rc = launch_ok("k_vertex_setup_views"))) break;
+        }
+        s->kernel_launches[light ? KS_SHADOW : KS_RASTER]++;
+        if (light) launch_raster_views<PassLightDepth>(s, rgrid, vb);
+        else { pipe.raster_views(s, rgrid, vb); s->kernel_launches[KS_SHADE]++; }
+        rc = launch_ok("k_raster_views");
+    }
+    s->cur = keep;
+    return rc;
+}
+
+// mode: kModeDepthOnly (K4), kModeVisibility (K3 alone) or a pipeline id (K3 + K5 fused).
+int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms& u, bool fresh_rgb) {
+    const bool depth_only = mode == kModeDepthOnly;
+    RasterArgs a = raster_args(s, depth_only, epoch, fresh, s->overlapping);
     ShadeArgs sa = shade_args(s, fresh_rgb);
-    // centre-out launch order shortens a lone frame's tail; overlapped batches do better in plain row order, where one
-    // frame's cheap border tiles run beside the previous frame's heavy ones (measured: profiles/README.md)
-    a.tile_order = s->tile_order + (s->overlapping ? (size_t)s->tiles_x * s->tiles_y : 0);
+    // (tile order: centre-out shortens a lone frame's tail; overlapped batches do better in plain row order, where one
+    // frame's cheap border tiles run beside the previous frame's heavy ones — measured: profiles/README.md)
     dim3 grid(s->tiles_x * s->tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
     // CTA shape: 256 threads for a lone frame, 128 for overlapped batches (k_raster.cuh)

@@ -108,8 +108,11 @@ def pinned_empty(shape, dtype):
         def __init__(self, ptr):
             self.ptr = ptr
 
-        def __del__(self):
-            lib().tr_host_free(self.ptr)
+        def __del__(self, _lib=lib):
+            try:
+                _lib().tr_host_free(self.ptr)
+            except Exception:           # interpreter shutdown: the module globals may already be gone
+                pass
 
     buf = (ctypes.c_uint8 * max(n, 1)).from_address(p)
     buf._owner = _Owner(p)
