@@ -128,6 +128,11 @@ int tr_scene_read_ao(tr_scene* s, uint32_t* accum_host);
  *                             needs no handles.  Maps the peers' accumulators; call again after the set of ranks changes
  *   tr_scene_ao_reduce_peers  collective, asynchronous on the scene stream: every rank calls it once per reduction.  A
  *                             rank that never arrives makes the others time out after 10 s: tr_scene_read_ao then fails
+ *                             and keeps failing until tr_scene_ao_open_peers is called again on every rank (it resets the
+ *                             barrier flags; the ranks must synchronise between it and the next reduction).  The kernel's
+ *                             barrier needs the 148 CTAs of every rank's launch resident at the same time: true for one
+ *                             rank per GPU (CTAs are dispatched in index order and a CTA only waits for its own index on
+ *                             the other ranks), and for at most two scenes sharing one GPU
  *   tr_scene_ao_close_peers   unmaps (also done by tr_scene_destroy) */
 int tr_scene_ao_ipc_handle(tr_scene* s, void* handle64);
 int tr_scene_ao_open_peers(tr_scene* s, const void* handles, uint32_t world, uint32_t rank);
@@ -136,7 +141,7 @@ int tr_scene_ao_close_peers(tr_scene* s);
 /* ---- native multi-GPU driver: one host process, one scene per device (tinyr_multi.inc) -------------------------------
  * The reference's process entry (main.rs:12-36) drives one Scene; these drive the two batch modes that shard naturally
  * over the devices of one box without Python, torch.distributed or NCCL.  `devices` lists CUDA ordinals (a device may
- * appear twice: two scenes on one GPU, which lets a single-GPU box exercise the sharded paths).
+ * appear twice — not more often — : two scenes on one GPU, which lets a single-GPU box exercise the sharded paths).
  *   tr_multi_render_views  device i renders views [i n / G, (i + 1) n / G); checksums / frames (optional, host, n entries
  *                          in VIEW order) are written by the devices directly; no data-path exchange
  *   tr_multi_render_ao     occlusion pipeline: device i accumulates lights [i n / G, (i + 1) n / G), then the accumulators

@@ -76,7 +76,7 @@ def test_peer_reduction_with_one_rank_is_the_identity(tinyr):
 
 def _device_lists():
     n = _gpu_count()
-    lists = [[0], [0, 0], [0, 0, 0]]
+    lists = [[0], [0, 0]]           # (two scenes per GPU is the limit: the exchange kernels of all entries must be co-resident)
     if n >= 2:
         lists += [[0, 1]]
     if n >= 4:

@@ -165,9 +165,12 @@ class Scene:
         self._h = h
         return self
 
-    def close(self):
+    def close(self, _lib=lib):
         if getattr(self, "_h", None):
-            lib().tr_scene_destroy(self._h)
+            try:
+                _lib().tr_scene_destroy(self._h)
+            except Exception:           # interpreter shutdown: the module globals may already be gone
+                pass
             self._h = None
 
     __del__ = close
@@ -343,9 +346,12 @@ class MultiScene:
         _check(lib().tr_multi_create(ctypes.byref(h), ctypes.byref(d), dev.ctypes.data, len(dev)))
         self._h = h
 
-    def close(self):
+    def close(self, _lib=lib):
         if getattr(self, "_h", None):
-            lib().tr_multi_destroy(self._h)
+            try:
+                _lib().tr_multi_destroy(self._h)
+            except Exception:
+                pass
             self._h = None
 
     __del__ = close
