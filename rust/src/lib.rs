@@ -9,6 +9,9 @@ use std::ffi::{c_char, c_int, c_void, CStr, CString};
 pub struct tr_scene { _private: [u8; 0] }
 
 #[repr(C)]
+pub struct tr_multi { _private: [u8; 0] }
+
+#[repr(C)]
 #[derive(Clone, Copy)]
 pub struct tr_image { pub rgb8_topdown: *const u8, pub width: u32, pub height: u32 }
 
@@ -47,6 +50,15 @@ extern "C" {
     pub fn tr_scene_render_ao(s: *mut tr_scene, lights_xyz: *const f32, n: u32, reset: c_int, accum_host: *mut u32) -> c_int;
     pub fn tr_scene_ao_device_buffer(s: *mut tr_scene, ptr: *mut *mut c_void, n: *mut usize) -> c_int;
     pub fn tr_scene_diagnostics(s: *mut tr_scene, out: *mut u64) -> c_int;
+    pub fn tr_host_alloc(bytes: usize) -> *mut c_void;
+    pub fn tr_host_free(p: *mut c_void);
+    pub fn tr_host_invalidate(p: *mut c_void, bytes: usize) -> c_int;
+    pub fn tr_multi_create_from_dir(out: *mut *mut tr_multi, asset_dir: *const c_char, pipeline: *const c_char, width: u32, height: u32,
+                                    devices: *const i32, n_devices: u32, ring: u32) -> c_int;
+    pub fn tr_multi_destroy(m: *mut tr_multi);
+    pub fn tr_multi_set_camera(m: *mut tr_multi, from: *const f32, at: *const f32, up: *const f32) -> c_int;
+    pub fn tr_multi_render_views(m: *mut tr_multi, views: *const tr_view, n: u32, checksums: *mut u64, frames: *mut u8) -> c_int;
+    pub fn tr_multi_render_ao(m: *mut tr_multi, lights_xyz: *const f32, n: u32, accum_host: *mut u32) -> c_int;
     pub fn tr_write_tga(path: *const c_char, rgb8_topdown: *const u8, width: u32, height: u32, rle: c_int) -> c_int;
     pub fn tr_last_error() -> *const c_char;
 }
@@ -107,4 +119,56 @@ impl Scene {
 
 impl Drop for Scene {
     fn drop(&mut self) { unsafe { tr_scene_destroy(self.h) } }
+}
+
+// ---- the shader-trait surface ------------------------------------------------------------------------------------
+// The reference's pluggable unit is `ShaderPass { prepare, vertex, fragment }` (src/scene/shader.rs:84-88): three boxed
+// closures over a shared `Buffer`, assembled per pipeline name by `ShaderPipeline::new` (shader.rs:97-112).  The backend
+// keeps the three roles, as compile-time roles of one C++ struct per pipeline (csrc/pipelines/*.cuh):
+//
+//     prepare   host (K0)    fn(&mut Uniforms, w, h, light, from, at, up) -> status       shader.rs:55-63  `Prepare`
+//     vertex    device (K1)  fn(&Uniforms, &VertexIn, &mut [f32; 24] varyings)            shader.rs:66-72  `VertexShader`
+//     fragment  device (K5)  fn(&ShadeArgs, &Uniforms, &FragmentIn) -> packed RGB         shader.rs:75-80  `FragmentShader`
+//
+// Device code cannot be supplied from Rust at run time, so on this side the surface is descriptive: the table below
+// mirrors csrc/pipeline_table.cuh (same order = same ids), and `Scene::from_dir(.., name)` / `tr_scene_set_pipeline`
+// select an entry by name exactly like `ShaderPipeline::new`.  Adding a pipeline means one header under csrc/pipelines/
+// plus one line in TR_PIPELINES — and one line here.
+
+/// Which host-side prepare a pass runs (shader.rs:183-279).
+#[derive(Clone, Copy, Debug, PartialEq, Eq)]
+pub enum Prepare { Default, ShadowPass1, ShadowPass2 }
+
+/// One pass of a pipeline, by its three roles.
+#[derive(Clone, Copy, Debug)]
+pub struct ShaderPass {
+    pub prepare: Prepare,
+    /// whether the vertex role culls back faces (pass 1 of shadow / occlusion does not, shader.rs:671-692)
+    pub vertex_culls: bool,
+    /// number of f32 varyings the vertex role hands to the fragment role per polygon
+    pub varying_words: u32,
+    /// maps the fragment role samples: texture, normal_map, normal_map_tangent, specular_map
+    pub maps: [bool; 4],
+}
+
+/// A named pipeline = its passes (shader.rs:97-112).
+#[derive(Clone, Copy, Debug)]
+pub struct ShaderPipeline { pub name: &'static str, pub alias: Option<&'static str>, pub passes: &'static [ShaderPass] }
+
+const LIGHT_DEPTH: ShaderPass = ShaderPass { prepare: Prepare::ShadowPass1, vertex_culls: false, varying_words: 0, maps: [false; 4] };
+
+/// Same order as TR_PIPELINES in csrc/pipeline_table.cuh.
+pub const PIPELINES: &[ShaderPipeline] = &[
+    ShaderPipeline { name: "default", alias: None, passes: &[ShaderPass { prepare: Prepare::Default, vertex_culls: true, varying_words: 3, maps: [true, false, false, false] }] },
+    ShaderPipeline { name: "phong", alias: None, passes: &[ShaderPass { prepare: Prepare::Default, vertex_culls: true, varying_words: 3, maps: [true, false, false, false] }] },
+    ShaderPipeline { name: "normal_map", alias: Some("true_normal"), passes: &[ShaderPass { prepare: Prepare::Default, vertex_culls: true, varying_words: 0, maps: [true, true, false, false] }] },
+    ShaderPipeline { name: "specular", alias: None, passes: &[ShaderPass { prepare: Prepare::Default, vertex_culls: true, varying_words: 0, maps: [true, true, false, true] }] },
+    ShaderPipeline { name: "darboux", alias: None, passes: &[ShaderPass { prepare: Prepare::Default, vertex_culls: true, varying_words: 21, maps: [true, false, true, false] }] },
+    ShaderPipeline { name: "shadow", alias: None, passes: &[LIGHT_DEPTH, ShaderPass { prepare: Prepare::ShadowPass2, vertex_culls: true, varying_words: 3, maps: [true, false, false, false] }] },
+    ShaderPipeline { name: "occlusion", alias: None, passes: &[LIGHT_DEPTH, ShaderPass { prepare: Prepare::ShadowPass2, vertex_culls: true, varying_words: 0, maps: [false; 4] }] },
+];
+
+/// `ShaderPipeline::new`'s name lookup (shader.rs:100-108), with the README's `true_normal` spelling.
+pub fn pipeline_by_name(name: &str) -> Option<&'static ShaderPipeline> {
+    PIPELINES.iter().find(|p| p.name == name || p.alias == Some(name))
 }
