@@ -233,7 +233,7 @@ def test_occlusion_division_forms_agree(tinyr):
     lights, _ = tinyr.generate_ao_lights(model.positions, 12)
     lf, la, up, _ = assets.view_vectors(0.4, 0.0)
     sums, frames = [], []
-    for flags in (0, 1, 4):                 # 1: range-tested form everywhere; 4: every predicted sample index recomputed exactly
+    for flags in (0, 1):
         s = Scene(w, h, model, "occlusion", ring=2)
         s.set_debug_flags(flags)
         s.set_camera(lf, la, up)
@@ -243,9 +243,8 @@ def test_occlusion_division_forms_agree(tinyr):
         assert s.diagnostics()["w_zero"] == 0
         s.close()
     assert sums[0].sum() > 0
-    for k in (1, 2):
-        assert np.array_equal(sums[0], sums[k]), k
-        assert np.array_equal(frames[0], frames[k]), k
+    assert np.array_equal(sums[0], sums[1])
+    assert np.array_equal(frames[0], frames[1])
 
 
 def _fuzz_views(rng, n, close=False):
@@ -437,7 +436,7 @@ def test_config4_render_ao_at_4k_matches_oracle(tinyr, oracle):
     o.set_camera(lf, la, up)
     want = o.render_ao(lights)
     assert o.diagnostics()["shadow_index_oob"] == 0
-    for ring, flags in ((8, 0), (1, 0), (8, 1), (8, 4)):
+    for ring, flags in ((8, 0), (1, 0), (8, 1)):
         g = Scene(3840, 2160, m, "occlusion", ring=ring)
         g.set_debug_flags(flags)
         g.set_camera(lf, la, up)

@@ -101,6 +101,15 @@ __device__ __forceinline__ float shadow_lookup(const float* shadow, f3 s, uint32
     return __ldg(&shadow[min(idx, n_px)]);      // shadow[n_px] is a sentinel holding the cleared value (f32::MIN)
 }
 
+// A note on what was tried here in r2 and measured not to pay (profiles/README.md "AO index predictor"): of every sample
+// the reference keeps only two rounded integers, so the sample's rows were predicted as (rows at wp) + (rows . step_k from
+// K0), divided with one MUFU.RCP, and the nearest integer accepted only when farther than a proven per-pixel bound eps from
+// the rounding boundary, recomputing the rest the reference's way: 22 instead of 45 instructions per accepted sample.  But
+// the reference's own rounding noise (5 roundings per term of a row whose terms reach 4,000 at 4K, times x / w up to 3,840)
+// already puts eps at 6.5e-3 px in x and 3.7e-3 in y, so 2 % of the samples are undecided — with 32 lanes and 8 samples per
+// group practically every warp runs the 65-instruction recomputation loop 1-2 times per group, which eats the saving:
+// k_ao_accumulate 50.1 us against 49.3, AO batch 17.64 k against 17.87 k passes/s.  Bit-identical (all AO parity tests
+// passed with it), not faster; removed.
 #ifndef TR_AO_GROUP
 #define TR_AO_GROUP 8
 #endif
@@ -141,78 +150,25 @@ __device__ __forceinline__ uint32_t occlusion_gray(const float* shadow, const Un
     const bool untested = reach_a <= 1024.0f && w_base >= 0x1p-60f && w_base <= 0x1p60f && reach <= 0.5f * w_base &&
                           x_base + reach_x <= (float)(u.width - 1u) * w_least && y_base + reach_y <= (float)(u.height - 1u) * w_least &&
                           (u.debug_flags & 1u) == 0u;
-    // ---- the guarded index predictor (hot form) ----------------------------------------------------------------------
-    // Of every sample the reference only keeps two rounded integers: ix = round(x / w), iy = round(y / w) with (x, y, w) =
-    // rows 0, 1, 3 of shadow * (wp + step_k, 1), every operation rounded to f32 in its own order.  Forming those rows the
-    // reference's way costs 21 instructions per sample and the two exact quotients another 9.  The predictor forms
-    //     X~ = X0 + dx_k,  Y~ = Y0 + dy_k,  W~ = W0 + dw_k          (X0.. = the rows at wp, dx_k.. = rows . step_k from K0)
-    //     x~ = X~ * rcp(W~),  y~ = Y~ * rcp(W~)
-    // and takes n = nearest integer to x~ — but only when x~ is farther than eps_x from the rounding boundary n +- 1/2,
-    // where eps_x bounds |x~ - RN(x_ref / w_ref)| for THIS pixel; otherwise (about 2 % of the samples at 4K) the sample is
-    // recomputed the reference's way below.  The accepted index therefore equals the reference's by construction.
-    // Bound, with u = 2^-24, T_r = sum_i |m_ri| (|wp_i| + 0.0201) + |m_r3| <= rowsum_r * span + |m_r3|:
-    //   * the reference's row value carries at most 5 roundings per term (wp + step, product, <= 3 sums):
-    //     |x_ref - x*| <= 5.01 u T_x; ours 4 per term for X0, one for dx_k, one for the sum: |X~ - x*| <= 5.2 u T_x; together
-    //     E_x = 10.3 u T_x, and likewise E_w = 10.3 u T_w;
-    //   * |X~/W~ - x_ref/w_ref| <= (E_x + xa E_w) / w_least with xa >= |x_ref / w_ref| (xa = width: `untested` above) and
-    //     w_least <= |W~|, |w_ref| (same argument as for `reach`);
-    //   * the reference rounds its quotient once (u), ours is a product (u) with a reciprocal of relative error <= 2^-22 (4 u):
-    //     <= 6.2 u xa in all.
-    //   eps_x = (10.3 u (T_x + width T_w)) / w_least + 6.2 u width, evaluated upwards (factor 1.05), and the same for y.
-    // x >= 0 for every sample (X0 - reach_x >= 0, W > 0), so `f32::round() as u32` is the nearest integer away from ties,
-    // and a tie (|x~ - n| = 1/2) never passes the test.  n is read off the mantissa of x~ + 1.5 * 2^23.
-    const float X0 = ((sm[0] * wp.x + sm[1] * wp.y) + sm[2] * wp.z) + sm[3];
-    const float Y0 = ((sm[4] * wp.x + sm[5] * wp.y) + sm[6] * wp.z) + sm[7];
-    const float W0 = ((sm[12] * wp.x + sm[13] * wp.y) + sm[14] * wp.z) + sm[15];
-    const float t_w = u.ao_w_rowsum * span + fabsf(sm[15]);
-    const float inv_w_least = 1.05f / w_least;              // (only used when `untested` holds: w_least >= w_base / 2 > 0)
-    const float wf = (float)u.width, hf = (float)u.height;
-    const float eps_x = (0x1.4cp-21f * ((u.ao_x_rowsum * span + fabsf(sm[3])) + wf * t_w)) * inv_w_least + 0x1.9p-22f * wf;   // 10.3 u = 1.2875 * 2^-21, 6.2 u = 1.55 * 2^-22
-    const float eps_y = (0x1.4cp-21f * ((u.ao_y_rowsum * span + fabsf(sm[7])) + hf * t_w)) * inv_w_least + 0x1.9p-22f * hf;
-    const float thr_x = 0.5f - 0x1p-18f - eps_x, thr_y = 0.5f - 0x1p-18f - eps_y;
-    const bool predict = untested && W0 > 0.0f && X0 - reach_x >= 0.0f && Y0 - reach_y >= 0.0f && thr_x > 0.25f && thr_y > 0.25f;
-    constexpr float kMagic = 12582912.0f;                   // 1.5 * 2^23: x + kMagic has the nearest integer to x in its low mantissa bits
-    const uint32_t index_bias = (0u - 0x4B400000u) * (u.width + 1u);           // removes kMagic's bit pattern from iy * width + ix
     auto samples = [&](auto untested_c) {
         constexpr bool UNTESTED = decltype(untested_c)::value;
         // Groups of kAoGroup samples: all shadow-buffer gathers of a group are issued before the first one is used.
-        // The hot form is unrolled completely, so the 16 offsets are constant-bank operands of the additions.
+        // The untested form is unrolled completely, so the 16 steps are constant-bank operands of the additions.
 #pragma unroll (UNTESTED ? 16 / kAoGroup : 1)
         for (int k0 = 0; k0 < 16; k0 += kAoGroup) {
             float sv[kAoGroup];
-            uint32_t redo = 0u;                             // samples of the group whose predicted index is not proven
 #pragma unroll
             for (int j = 0; j < kAoGroup; ++j) {
+                f3 sp = wp + u.ao_step[k0 + j];
+                const f4 sh = xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f});
                 if (UNTESTED) {
-                    const float X = X0 + u.ao_dx[k0 + j], Y = Y0 + u.ao_dy[k0 + j], W = W0 + u.ao_dw[k0 + j];
-                    float r;
-                    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(W));      // MUFU.RCP
-                    const float xt = X * r, yt = Y * r;
-                    const float vx = xt + kMagic, vy = yt + kMagic;
-                    const float ex = xt - (vx - kMagic), ey = yt - (vy - kMagic);
-                    if (!(fabsf(ex) < thr_x && fabsf(ey) < thr_y)) redo |= 1u << j;
-                    sv[j] = __ldg(&shadow[__float_as_uint(vy) * u.width + __float_as_uint(vx) + index_bias]);
+                    const SharedDivisor d = shared_divisor(sh.w);
+                    // z of the sample is not used
+                    sv[j] = __ldg(&shadow[round_u32(quotient(sh.x, d)) + round_u32(quotient(sh.y, d)) * u.width]);
                 } else {
-                    f3 sp = wp + u.ao_step[k0 + j];
-                    const f4 sh = xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f});
                     f3 sc = dehomog_shared(sh, ok);
                     count_if_zero(dl.w_zero, sh.w);
                     sv[j] = shadow_lookup(shadow, sc, u.width, n_px, dl);
-                }
-            }
-            if (UNTESTED) {
-                if (u.debug_flags & 4u) redo = (1u << kAoGroup) - 1u;
-                // the reference's own arithmetic for the samples the predictor could not decide (z of the sample is not used;
-                // no range test, no counts: `untested` proves w inside the divisor's range and the indices inside the buffer)
-                while (redo) {
-                    const int j = __ffs(redo) - 1;
-                    redo &= redo - 1u;
-                    f3 sp = wp + u.ao_step[k0 + j];
-                    const f4 sh = xform(u.shadow, f4{sp.x, sp.y, sp.z, 1.0f});
-                    const SharedDivisor d = shared_divisor(sh.w);
-                    const float v = __ldg(&shadow[round_u32(quotient(sh.x, d)) + round_u32(quotient(sh.y, d)) * u.width]);
-#pragma unroll
-                    for (int q = 0; q < kAoGroup; ++q) sv[q] = q == j ? v : sv[q];
                 }
             }
 #pragma unroll
@@ -224,7 +180,7 @@ __device__ __forceinline__ uint32_t occlusion_gray(const float* shadow, const Un
             }
         }
     };
-    if (predict) samples(std::true_type{}); else samples(std::false_type{});
+    if (untested) samples(std::true_type{}); else samples(std::false_type{});
     return cast_u8(occ * 255.0f + (1.0f - occ) * 0.0f);
 }
 

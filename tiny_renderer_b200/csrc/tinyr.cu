@@ -386,6 +386,18 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
     return TR_OK;
 }
 
+// CUDA loads kernels lazily, and loading one may wait for the device to go idle: a rank's exchange kernel spinning at its
+// barrier while another rank's FIRST launch of the same kernel is still being loaded would never be released (seen with
+// two scenes on one GPU).  Every variant is therefore loaded when the peers are opened.
+void preload_peer_kernels() {
+    cudaFuncAttributes fa;
+    cudaFuncGetAttributes(&fa, k_ao_reduce_peers<0>);
+    cudaFuncGetAttributes(&fa, k_ao_reduce_peers<2>);
+    cudaFuncGetAttributes(&fa, k_ao_reduce_peers<4>);
+    cudaFuncGetAttributes(&fa, k_ao_reduce_peers<8>);
+    cudaGetLastError();
+}
+
 void close_peers(tr_scene* s) {
     for (uint32_t r = 0; r < s->peer_world; ++r)
         if (s->peer_ipc && r != s->peer_rank && s->peer_buf[r]) cudaIpcCloseMemHandle(s->peer_buf[r]);

@@ -128,11 +128,6 @@ inline int prepare_camera_with_shadow(Uniforms& u, uint32_t width, uint32_t heig
         for (int k = 0; k < 16; ++k) {
             float a = angle_coef * (float)k;
             u.ao_step[k] = xform(rot, f3{sinf(a), 0.0f, cosf(a)}) * step;
-            const f3 st = u.ao_step[k];
-            const float* sm = u.shadow.m;
-            u.ao_dx[k] = (float)((double)sm[0] * st.x + (double)sm[1] * st.y + (double)sm[2] * st.z);
-            u.ao_dy[k] = (float)((double)sm[4] * st.x + (double)sm[5] * st.y + (double)sm[6] * st.z);
-            u.ao_dw[k] = (float)((double)sm[12] * st.x + (double)sm[13] * st.y + (double)sm[14] * st.z);
         }
     }
     return PREP_OK;

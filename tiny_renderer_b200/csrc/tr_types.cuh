@@ -26,13 +26,9 @@ struct Uniforms {
     f3 camera_direction;
     f3 t_light;
     f3 ao_step[16];               // (rot * (sin a_k, 0, cos a_k)) * 0.02   (shader.rs:920-929)
-    // rows 0, 1 and 3 of `shadow` applied to the 16 steps (formed in double, rounded once): how far a sample's homogeneous
-    // x, y, w lie from those of the fragment itself.  Only the guarded index predictor of k_shade.cuh uses them.
-    float ao_dx[16], ao_dy[16], ao_dw[16];
     float ao_w_rowsum;            // |s30| + |s31| + |s32| of `shadow` (bounds how far a sample's w moves; k_shade.cuh)
     float ao_x_rowsum, ao_y_rowsum;   // the same sums over rows 0 and 1 (bound the samples' shadow-buffer coordinates)
-    uint32_t debug_flags;         // bit 0: occlusion samples always take the range-tested division; bit 2: every predicted
-                                  // sample index is recomputed exactly (k_shade.cuh)
+    uint32_t debug_flags;         // bit 0: occlusion samples always take the range-tested division
     uint32_t width, height;
     uint32_t n_triangles;
     uint32_t epoch;               // renders since the last clear (see Key below)
