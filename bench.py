@@ -325,7 +325,8 @@ def raster_kernel(pipe, threads):
 
 
 def setup_kernel(pipe):
-    return "k_vertex_setup<%s>" % PIPE_STRUCT[pipe]
+    """The vertex set-up kernel: one instantiation for the camera pass of every pipeline, one for the light pass."""
+    return "k_vertex_setup<true>" if pipe == "light_depth" else "k_vertex_setup<false>"
 
 
 def ncu_kernel_summary(want):
@@ -337,7 +338,10 @@ def ncu_kernel_summary(want):
     for pipe, st in PIPE_STRUCT.items():
         if st in want:
             wants.append(wants[0].replace("k_raster<" + st, "k_raster<%d" % LEGACY_ID[pipe]))
-            wants.append(wants[0].replace("k_vertex_setup<" + st, "k_vertex_setup<%d" % (1 if pipe == "light_depth" else 0)))
+    if wants[0] == "k_vertex_setup<false>":     # earlier spellings of the same kernel in committed captures
+        wants += ["k_vertex_setup<0>", "k_vertex_setup<PipelineDarboux>", "k_vertex_setup<PipelinePhong>"]
+    if wants[0] == "k_vertex_setup<true>":
+        wants += ["k_vertex_setup<1>", "k_vertex_setup<PassLightDepth>"]
     table, src = ncu_summaries()
     for w in wants:
         for k, v in table.items():

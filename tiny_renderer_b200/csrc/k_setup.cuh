@@ -3,7 +3,7 @@
 // (/root/reference/src/scene/shader.rs:285-316, 349-384, 416-437, 475-496, 549-595, 671-692, 711-747,
 // 809-830, 849-870), their helpers (shader.rs:116-165) and the bounding box of scene.rs:232-239.
 #pragma once
-#include "pipeline.cuh"
+#include "pipeline_table.cuh"
 
 namespace tr {
 
@@ -18,11 +18,15 @@ struct SetupOut {
     Bins bins;        // K2: per-cell polygon lists for the raster kernel that follows
 };
 
-// PIPE: the pipeline whose `vertex` role writes the varyings (pipeline.cuh); PassLightDepth = shadow/occlusion pass 1 —
-// no culling, transform by u.shadow, no varyings.
-template <class PIPE>
-__device__ __forceinline__ void vertex_setup(const float4* __restrict__ geom, const SetupOut& out, const Uniforms& u, unsigned long long* diag) {
-    constexpr bool LIGHT_PASS = PIPE::id == kModeDepthOnly;
+// LIGHT_PASS: shadow/occlusion pass 1 — no culling, transform by u.shadow, no varyings.  Otherwise `pipeline` selects the
+// pipeline whose `vertex` role (pipeline.cuh) writes the varyings.  The camera pass is ONE kernel for all pipelines, with a
+// switch over the vertex roles generated from the pipeline list, not one instantiation per pipeline: a kernel per pipeline
+// was measured in r2 (smaller kernels, 792-1,552 instructions instead of 2,080) and cost the phong + darboux view batch
+// 5 % (266 vs 279 Gpx/s; each pipeline alone unchanged) — two scenes with different pipelines then keep two set-up
+// kernels resident beside their tile kernels, and the SMs' 32 KB L1.5 instruction cache is already oversubscribed.
+template <bool LIGHT_PASS>
+__device__ __forceinline__ void vertex_setup(const float4* __restrict__ geom, const SetupOut& out, const Uniforms& u, int pipeline,
+                                             unsigned long long* diag) {
     // The tile kernel behind this one is launched with programmatic stream serialization (tinyr.cu: launch_raster): let
     // it start now; it waits for this grid's completion before it touches anything written here.
     asm volatile("griddepcontrol.launch_dependents;");
@@ -111,7 +115,7 @@ __device__ __forceinline__ void vertex_setup(const float4* __restrict__ geom, co
     rec[2] = make_float4(rz[2], __int_as_float(drawn ? kFlagDrawn : 0u), g[9], g[10]);
     rec[3] = make_float4(g[11], g[12], g[13], g[14]);
     if constexpr (!LIGHT_PASS) {
-        if (!drawn || out.var == nullptr || PIPE::varying_words == 0) return;
+        if (!drawn || out.var == nullptr) return;
         float v[kVarWords];
 #pragma unroll
         for (int k = 0; k < kVarWords; ++k) v[k] = 0.0f;
@@ -119,28 +123,40 @@ __device__ __forceinline__ void vertex_setup(const float4* __restrict__ geom, co
 #pragma unroll
         for (int i = 0; i < 3; ++i) { in.p[i] = p[i]; in.n[i] = f3{g[15 + 3 * i], g[16 + 3 * i], g[17 + 3 * i]}; }
         in.face_normal = face_normal;
-        PIPE::vertex(u, in, v, diag);
+        int words = 0, role = pipeline;
+        switch (pipeline) {                 // which vertex role this pipeline runs (pipelines may share one: shadow runs phong's)
+#define TR_X(N) case kPipe##N: role = Pipeline##N::vertex_role; words = Pipeline##N::varying_words; break;
+            TR_PIPELINES(TR_X)
+#undef TR_X
+        }
+        if (words == 0) return;             // nothing beyond the shared transform / uv store
+        switch (role) {                     // the vertex role of every pipeline in the table that has one of its own
+#define TR_X(N) case kPipe##N: if constexpr (Pipeline##N::vertex_role == kPipe##N && Pipeline##N::varying_words > 0) Pipeline##N::vertex(u, in, v, diag); break;
+            TR_PIPELINES(TR_X)
+#undef TR_X
+        }
         float4* var = out.var + (size_t)t * 6;
 #pragma unroll
-        for (int k = 0; k < (PIPE::varying_words + 3) / 4; ++k) var[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+        for (int k = 0; k < kVarWords / 4; ++k)
+            if (4 * k < words) var[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
     }
 }
 
-template <class PIPE>
-__global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__ geom, const SetupOut out, const Uniforms u,
+template <bool LIGHT_PASS>
+__global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__ geom, const SetupOut out, const Uniforms u, int pipeline,
                                                      unsigned long long* diag) {
-    vertex_setup<PIPE>(geom, out, u, diag);
+    vertex_setup<LIGHT_PASS>(geom, out, u, pipeline, diag);
 }
 
 // Several views in one launch (see k_raster_views): blockIdx.y selects the view's uniforms and frame slot.
 constexpr int kMaxSetupViews = 8;
 struct SetupViewArgs { SetupOut out; Uniforms u; };
 struct SetupViewBatch { SetupViewArgs v[kMaxSetupViews]; };
-template <class PIPE>
-__global__ void __launch_bounds__(128) k_vertex_setup_views(const float4* __restrict__ geom, const __grid_constant__ SetupViewBatch b,
+template <bool LIGHT_PASS>
+__global__ void __launch_bounds__(128) k_vertex_setup_views(const float4* __restrict__ geom, const __grid_constant__ SetupViewBatch b, int pipeline,
                                                            unsigned long long* diag) {
     const SetupViewArgs& v = b.v[blockIdx.y];
-    vertex_setup<PIPE>(geom, v.out, v.u, diag);
+    vertex_setup<LIGHT_PASS>(geom, v.out, v.u, pipeline, diag);
 }
 
 }  // namespace tr

@@ -9,7 +9,7 @@
 //     static u32  fragment(const ShadeArgs&, const Uniforms&, const FragmentIn&)         device (K5; `FragmentShader`, shader.rs:75-80)
 //
 // plus a few constants (name, optional alias, whether a light-depth pass runs first, how many varying words the vertex
-// role writes).  pipeline_table.cuh lists the structs once; the name lookup (ShaderPipeline::new, shader.rs:97-112), the
+// role writes, whose vertex role it runs when it shares one).  pipeline_table.cuh lists the structs once; the name lookup (ShaderPipeline::new, shader.rs:97-112), the
 // kernel instantiations (k_vertex_setup<PIPE>, k_raster<PIPE, THREADS>) and the host dispatch are all generated from
 // that list, so adding a pipeline is one new header plus one line of the table.
 //

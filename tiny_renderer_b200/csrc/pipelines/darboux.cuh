@@ -9,6 +9,7 @@ struct PipelineDarboux {
     static constexpr const char* name = "darboux";
     static constexpr const char* alias = nullptr;
     static constexpr bool light_pass = false;
+    static constexpr int vertex_role = kPipeDarboux;
     static constexpr int varying_words = 21;
     static constexpr bool heavy_fragment = true;        // 62 registers: the tile kernel keeps fewer CTAs per SM (k_raster.cuh)
 

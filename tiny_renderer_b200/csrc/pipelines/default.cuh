@@ -9,6 +9,7 @@ struct PipelineDefault {
     static constexpr const char* name = "default";
     static constexpr const char* alias = nullptr;
     static constexpr bool light_pass = false;
+    static constexpr int vertex_role = kPipeDefault;
     static constexpr int varying_words = 3;
     static constexpr bool heavy_fragment = false;
 

@@ -10,6 +10,7 @@ struct PipelineNormalMap {
     static constexpr const char* name = "normal_map";
     static constexpr const char* alias = "true_normal";        // README.md:18 names it so; the code matches "normal_map" (shader.rs:103)
     static constexpr bool light_pass = false;
+    static constexpr int vertex_role = kPipeNormalMap;
     static constexpr int varying_words = 0;
     static constexpr bool heavy_fragment = false;
 

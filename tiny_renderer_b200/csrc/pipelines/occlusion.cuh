@@ -11,6 +11,7 @@ struct PipelineOcclusion {
     static constexpr const char* name = "occlusion";
     static constexpr const char* alias = nullptr;
     static constexpr bool light_pass = true;            // pass 1: shader.rs:809-847
+    static constexpr int vertex_role = kPipeOcclusion;
     static constexpr int varying_words = 0;
     static constexpr bool heavy_fragment = false;
 

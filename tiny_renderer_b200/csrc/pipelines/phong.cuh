@@ -9,6 +9,7 @@ struct PipelinePhong {
     static constexpr const char* name = "phong";
     static constexpr const char* alias = nullptr;
     static constexpr bool light_pass = false;
+    static constexpr int vertex_role = kPipePhong;
     static constexpr int varying_words = 3;
     static constexpr bool heavy_fragment = false;
 

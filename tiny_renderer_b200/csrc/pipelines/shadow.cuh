@@ -10,6 +10,7 @@ struct PipelineShadow {
     static constexpr const char* name = "shadow";
     static constexpr const char* alias = nullptr;
     static constexpr bool light_pass = true;            // pass 1: shadow_pass_prepare_1 + no-cull vertex + depth-max fragment (shader.rs:671-709)
+    static constexpr int vertex_role = kPipePhong;        // pass 2 shares the phong vertex closure (shader.rs:711-747 == :349-384)
     static constexpr int varying_words = 3;
     static constexpr bool heavy_fragment = false;
 

@@ -9,6 +9,7 @@ struct PipelineSpecular {
     static constexpr const char* name = "specular";
     static constexpr const char* alias = nullptr;
     static constexpr bool light_pass = false;
+    static constexpr int vertex_role = kPipeSpecular;
     static constexpr int varying_words = 0;
     static constexpr bool heavy_fragment = false;
 

@@ -113,19 +113,14 @@ struct PipelineEntry {
     const char* alias;
     bool light_pass;
     int (*prepare)(Uniforms&, uint32_t, uint32_t, f3, f3, f3, f3);
-    void (*setup)(tr_scene*, dim3, const SetupOut&, const Uniforms&);
     void (*raster[2])(tr_scene*, dim3, const RasterArgs&, const ShadeArgs&, const Uniforms&);      // [0] lone-frame CTA shape, [1] batch shape
-    void (*setup_views)(tr_scene*, dim3, const SetupViewBatch&);                                   // several views per launch (small frames)
-    void (*raster_views)(tr_scene*, dim3, const ViewBatch&);
+    void (*raster_views)(tr_scene*, dim3, const ViewBatch&);                                       // several views per launch (small frames)
 };
-template <class PIPE> void launch_setup(tr_scene* s, dim3 grid, const SetupOut& out, const Uniforms& u);
 template <class PIPE, int T> void launch_raster(tr_scene* s, dim3 grid, const RasterArgs& a, const ShadeArgs& sa, const Uniforms& u);
-template <class PIPE> void launch_setup_views(tr_scene* s, dim3 grid, const SetupViewBatch& b);
 template <class PIPE> void launch_raster_views(tr_scene* s, dim3 grid, const ViewBatch& b);
 template <class PIPE> constexpr PipelineEntry pipeline_entry() {
-    return {PIPE::name, PIPE::alias, PIPE::light_pass, &PIPE::prepare, &launch_setup<PIPE>,
-            {&launch_raster<PIPE, kRasterThreads>, &launch_raster<PIPE, kRasterThreadsBatch>},
-            &launch_setup_views<PIPE>, &launch_raster_views<PIPE>};
+    return {PIPE::name, PIPE::alias, PIPE::light_pass, &PIPE::prepare,
+            {&launch_raster<PIPE, kRasterThreads>, &launch_raster<PIPE, kRasterThreadsBatch>}, &launch_raster_views<PIPE>};
 }
 const PipelineEntry kPipelines[kPipeCount] = {
 #define TR_X(N) pipeline_entry<Pipeline##N>(),
@@ -443,8 +438,9 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     S(s).bins.parity ^= 1u;                 // this pass fills the other counter set; the kernel zeroes the one just used
     S(s).cam.bins = S(s).bins;
     S(s).lit.bins = S(s).bins;
-    if (light_pass) launch_setup<PassLightDepth>(s, grid, S(s).lit, u);
-    else kPipelines[s->pipeline].setup(s, grid, S(s).cam, u);
+    // (the vertex roles of all pipelines live in one kernel: k_setup.cuh)
+    if (light_pass) k_vertex_setup<true><<<grid, 128, 0, s->stream>>>(s->geom, S(s).lit, u, s->pipeline, s->diag);
+    else k_vertex_setup<false><<<grid, 128, 0, s->stream>>>(s->geom, S(s).cam, u, s->pipeline, s->diag);
     return launch_ok("k_vertex_setup");
 }
 
@@ -476,14 +472,6 @@ void launch_raster(tr_scene* s, dim3 grid, const RasterArgs& a, const ShadeArgs&
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     cudaLaunchKernelEx(&cfg, k_raster<PIPE, T>, a, sa, u, S(s).rgb_map, S(s).rgb_map_top);
-}
-template <class PIPE>
-void launch_setup(tr_scene* s, dim3 grid, const SetupOut& out, const Uniforms& u) {
-    k_vertex_setup<PIPE><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->diag);
-}
-template <class PIPE>
-void launch_setup_views(tr_scene* s, dim3 grid, const SetupViewBatch& b) {
-    k_vertex_setup_views<PIPE><<<grid, 128, 0, s->stream>>>(s->geom, b, s->diag);
 }
 template <class PIPE>
 void launch_raster_views(tr_scene* s, dim3 grid, const ViewBatch& b) {
@@ -543,8 +531,8 @@ int run_views_multi(tr_scene* s, const uint32_t* slots, const Uniforms* lit, con
         }
         if (s->n_tri) {
             s->kernel_launches[KS_SETUP]++;
-            if (light) launch_setup_views<PassLightDepth>(s, sgrid, sb);
-            else pipe.setup_views(s, sgrid, sb);
+            if (light) k_vertex_setup_views<true><<<sgrid, 128, 0, s->stream>>>(s->geom, sb, s->pipeline, s->diag);
+            else k_vertex_setup_views<false><<<sgrid, 128, 0, s->stream>>>(s->geom, sb, s->pipeline, s->diag);
             if ((rc = launch_ok("k_vertex_setup_views"))) break;
         }
         s->kernel_launches[light ? KS_SHADOW : KS_RASTER]++;
