@@ -418,3 +418,24 @@ def test_k0_uniforms_equal_the_oracle_bit_for_bit(tinyr, oracle, pipeline):
                 if pipeline == "occlusion":
                     assert np.array_equal(ga["ao_step"].view(np.uint32), oa["ao_step"].view(np.uint32)), (w, h, trial)
         g.close()
+
+
+def test_hundreds_of_renders_without_clear(tinyr, oracle):
+    """The reference never clears by itself (scene.rs:151) and allows any number of renders on top of each other.  The
+    key's epoch field has 8 bits: past 255 renders the stored winners are folded into epoch 0 (k_collapse_epochs) and the
+    sequence goes on — all buffers still equal the oracle's after 300 renders of alternating views."""
+    from tiny_renderer_b200.scene import Scene
+    model = get_model("african_head")
+    w, h = 96, 80
+    g = Scene(w, h, model, "phong")
+    o = oracle.OracleScene(w, h, model, "phong")
+    g.clear(); o.clear()
+    views = [assets.view_vectors(0.3 * k, 0.5 + 0.2 * k) for k in range(5)]
+    for i in range(300):
+        lf, la, up, l = views[i % 5]
+        parity.drive(g, lf, la, up, l, clear=False)
+        parity.drive(o, lf, la, up, l, clear=False)
+        if i in (0, 7, 254, 255, 256, 257, 299):
+            st = parity.compare(g, o, rgb_frac=1.0)
+            assert st["depth_bits_differ"] == 0 and st["rgb_exact_frac"] == 1.0, (i, st)
+    g.close()

@@ -29,6 +29,22 @@ __global__ void __launch_bounds__(256) k_materialise_tiles(unsigned long long* k
     if (threadIdx.x == 0) tile_state[tile] = 0u;
 }
 
+// The epoch field of a key (renders since the last clear) has 8 bits.  The reference allows any number of renders without
+// a clear (scene.rs:151 never clears), so when the field would overflow every stored winner is moved to epoch 0 — all
+// that matters about an old winner is that it orders before whatever the NEXT render draws at the same depth — and the
+// scene continues at epoch 1.  One CTA per raster tile; tiles in the tile-level cleared state hold no keys.
+__global__ void __launch_bounds__(256) k_collapse_epochs(unsigned long long* keys, const uint32_t* tile_state, uint32_t width, uint32_t height) {
+    const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
+    if (tile_state[tile] != 0u) return;
+    for (int i = threadIdx.x; i < kTileW * kTileH; i += 256) {
+        uint32_t px = blockIdx.x * kTileW + i % kTileW, py = blockIdx.y * kTileH + i / kTileW;
+        if (px < width && py < height) {
+            unsigned long long k = keys[(size_t)py * width + px];
+            if (key_lo(k) != kNoTri) keys[(size_t)py * width + px] = (k & 0xFFFFFFFF00000000ull) | (key_lo(k) & kTriMask);
+        }
+    }
+}
+
 // Raw bottom-up views of the state the reference keeps in Buffer.z_buffer / visibility (derived from keys).
 __global__ void __launch_bounds__(256) k_unpack_keys(const unsigned long long* keys, float* depth, uint32_t* tri, size_t n_px) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -601,7 +601,14 @@ int run_ao_accumulate(tr_scene* s, const Uniforms& u, uint32_t n_covered) {
 // Scene::render (scene.rs:151-268): every pass = prepare, all polygons through the vertex stage, raster.
 int render_impl(tr_scene* s) {
     CU(cudaSetDevice(s->device));
-    if (s->epoch > kMaxEpoch) return fail(TR_ERR_UNSUPPORTED, "more than %u renders without tr_scene_clear", kMaxEpoch);
+    if (s->epoch > kMaxEpoch) {
+        // 255 renders without a clear: fold the epochs of the stored winners into epoch 0 and go on (k_misc.cuh)
+        Scoped sp(s, KS_CLEAR);
+        k_collapse_epochs<<<dim3(s->tiles_x, s->tiles_y), 256, 0, s->stream>>>(S(s).keys, S(s).tile_state, s->width, s->height);
+        int rc0 = launch_ok("k_collapse_epochs");
+        if (rc0) return rc0;
+        s->epoch = 1;
+    }
     int rc;
     Uniforms u{};
     u.n_triangles = s->n_tri; u.epoch = s->epoch;
