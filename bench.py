@@ -579,7 +579,7 @@ def run_views8k(rank, world, dev, model, head, dist, tstream):
             cov[name] = int((s.raw_visibility() != 0xFFFFFFFF).sum())
         tri = {"african_head": len(head.tri_idx), "diablo": len(model.tri_idx)}
         nbytes = sum(algorithmic_bytes(n_px, cov[k], tri[k], "specular")["frame"] for k in scenes) / 2
-        us = out["us_per_view"] * world          # device time per view on one GPU
+        us = out["us_per_view"]                  # device time per view on one GPU (each rank renders its own block)
         out["roofline"] = {"bound": "hbm", "algorithmic_bytes_per_view": nbytes, "us_per_view_per_gpu": us,
                            "achieved": nbytes / (us * 1e-6) / 1e9, "peak": peak,
                            "unit": "GB/s", "frac": nbytes / (us * 1e-6) / 1e9 / peak, "covered_px_view0": cov,
