@@ -883,6 +883,9 @@ def run_gpu(args, rank, world, local_rank):
                    "(the vertex set-up launches in between are inside that time); `alone` is the same kernel timed one launch at a time"
                    % (REPS, RING),
             "us_per_launch_sustained": alone_us[dom], "sustained": sustained,
+            "note": "time-to-solution against SURVEY.md 8(d)'s byte model (19 P + texels + geometry), not a DRAM utilisation: the tile "
+                    "kernel never writes the keys of untouched tiles nor rewrites zero tiles, so it moves far fewer bytes than the model "
+                    "(`traffic`) and a light pipeline can exceed 1.0 (phong); what binds it is instruction issue (`issue`)",
             "alone": {"achieved": k["achieved"], "frac": k["frac"], "us_per_launch": k["us_per_launch"],
                       "note": "one frame at a time on one stream (profiling mode): a lone launch leaves SMs idle behind its heaviest tiles"},
             "traffic": (steady or {}).get("dram_bytes_per_frame", k["traffic"]),
