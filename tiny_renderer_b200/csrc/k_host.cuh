@@ -13,6 +13,10 @@
 // No staging buffer, no host-side scatter: the host CPU does not touch a pixel.
 //
 // Rows of a tile are 192 bytes (64 px) at a 64-byte aligned offset, written as 12 x 16-byte stores by 12 adjacent lanes.
+// (A form with one warp per strip of four adjacent tiles — store instructions covering up to 512 contiguous bytes, so that
+// everything leaves as full 128-byte lines — was measured in r2 and is no faster: 62.8 / 64.9 / 66.8 Gpx/s end to end with
+// 8 / 16 / 32 CTAs against 65.3 / 63.6 / 65.0 for this form on the same box; SM-issued stores to host memory top out near
+// 47 GB/s here whatever their shape, a DMA copy reaches 54-57.)
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -86,86 +90,6 @@ __global__ void __launch_bounds__(kHostThreads) k_frame_to_host(const HostStoreA
             const int n = __popc(write & (rows >= 32 ? 0xffffffffu : ((1u << rows) - 1u)));
             rows_stored += n;
             bytes_stored += (unsigned long long)n * seg16 * 16;
-        }
-    }
-    if (lane == 0 && rows_stored) {
-        atomicAdd(&a.stats[0], bytes_stored);
-        atomicAdd(&a.stats[1], rows_stored);
-    }
-}
-
-// Second form of the same delivery: one warp per STRIP of kStripTiles horizontally adjacent tiles.  The rows of a strip are
-// kStripTiles x 192 contiguous bytes, so a warp's store instruction covers up to 512 contiguous bytes of the host frame
-// instead of one tile's 192 (= one full 128-byte line and a half one): the device -> host writes leave as full lines.
-// Pass 1 forms the row masks of the strip's tiles exactly as above (loads + ballots, nothing kept); pass 2 walks the rows
-// and stores the 16-byte columns whose tile has the row's bit set, re-reading them (L2 hits).
-constexpr int kStripTiles = 4;
-__global__ void __launch_bounds__(kHostThreads) k_frame_to_host_strips(const HostStoreArgs a) {
-    const int lane = threadIdx.x & 31;
-    const uint32_t warp = (blockIdx.x * kHostThreads + threadIdx.x) >> 5, n_warps = gridDim.x * kHostThreads / 32;
-    const size_t pitch = (size_t)a.width * 3;
-    const int sub = lane / 12, col = lane % 12;
-    const uint32_t strips_x = (a.tiles_x + kStripTiles - 1) / kStripTiles, tiles_y = a.n_tiles / a.tiles_x;
-    unsigned long long rows_stored = 0, bytes_stored = 0;
-    for (uint32_t strip = warp; strip < strips_x * tiles_y; strip += n_warps) {
-        const uint32_t ty = strip / strips_x, tx_first = (strip % strips_x) * kStripTiles;
-        const int ty0 = (int)ty * kTileH;
-        const int rows = min(kTileH, (int)a.height - ty0);
-        uint32_t now[kStripTiles], wr[kStripTiles];
-        bool zero[kStripTiles];
-        uint32_t any = 0u;
-#pragma unroll
-        for (int t = 0; t < kStripTiles; ++t) {
-            now[t] = wr[t] = 0u; zero[t] = true;
-            const uint32_t tx = tx_first + t;
-            if (tx >= a.tiles_x) continue;
-            const uint32_t tile = ty * a.tiles_x + tx;
-            const uint32_t prev = a.row_mask[tile];
-            zero[t] = a.rgb_zero[tile] != 0u;
-            if (!zero[t]) {
-                const int tx0 = (int)tx * kTileW;
-                const int seg16 = (min(kTileW, (int)a.width - tx0) * 3) / 16;
-                const bool active = sub < 2 && col < seg16;
-#pragma unroll 4
-                for (int i = 0; i < kTileH / 2; ++i) {
-                    const int r = 2 * i + sub;
-                    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-                    if (active && r < rows)
-                        v = __ldg(reinterpret_cast<const uint4*>(a.rgb + (size_t)(a.height - 1 - (ty0 + r)) * pitch + (size_t)tx0 * 3) + col);
-                    const unsigned b = __ballot_sync(0xffffffffu, (v.x | v.y | v.z | v.w) != 0u);
-                    if (b & 0x00000fffu) now[t] |= 1u << (2 * i);
-                    if (b & 0x00fff000u) now[t] |= 1u << (2 * i + 1);
-                }
-            }
-            wr[t] = (now[t] | prev) & (rows >= 32 ? 0xffffffffu : ((1u << rows) - 1u));
-            any |= wr[t];
-            if (lane == 0) {
-                if (now[t] != prev) a.row_mask[tile] = now[t];
-                const int n = __popc(wr[t]);
-                rows_stored += n;
-                bytes_stored += (unsigned long long)n * ((min(kTileW, (int)a.width - (int)tx * kTileW) * 3) / 16) * 16;
-            }
-        }
-        if (any == 0u) continue;
-        // 16-byte columns of the strip's row segment: tile t covers columns [12 t, 12 t + 12) (fewer in the frame's last tile)
-        const int x0 = (int)tx_first * kTileW;
-        const int ncols = (min(kStripTiles * kTileW, (int)a.width - x0) * 3) / 16;
-        for (int r = 0; r < rows; ++r) {
-            if (((any >> r) & 1u) == 0u) continue;
-            const size_t row_at = (size_t)(a.height - 1 - (ty0 + r)) * pitch + (size_t)x0 * 3;
-#pragma unroll
-            for (int step = 0; step < (kStripTiles * 12 + 31) / 32; ++step) {
-                const int c = step * 32 + lane;
-                const int t = c / 12;
-                uint32_t w = 0u;
-                bool z = true;
-#pragma unroll
-                for (int q = 0; q < kStripTiles; ++q) if (q == t) { w = wr[q]; z = zero[q]; }
-                if (c < ncols && ((w >> r) & 1u)) {
-                    const uint4 v = z ? make_uint4(0u, 0u, 0u, 0u) : __ldg(reinterpret_cast<const uint4*>(a.rgb + row_at) + c);
-                    st_host_v4(reinterpret_cast<uint4*>(a.dst + row_at) + c, v);
-                }
-            }
         }
     }
     if (lane == 0 && rows_stored) {
