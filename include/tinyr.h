@@ -159,6 +159,12 @@ tr_scene* tr_multi_scene(tr_multi* m, uint32_t i);
 int tr_multi_set_camera(tr_multi* m, const float look_from[3], const float look_at[3], const float up[3]);
 int tr_multi_render_views(tr_multi* m, const tr_view* views, uint32_t n_views, uint64_t* checksums, uint8_t* frames_rgb8_topdown);
 int tr_multi_render_ao(tr_multi* m, const float* light_dirs_xyz, uint32_t n_lights, uint32_t* accum_host);
+/* "nvls": the accumulators live in memory bound to one NVSwitch multicast object and are summed INSIDE the switch
+ * (multimem.ld_reduce / multimem.st, k_peer.cuh k_ao_reduce_nvls) — used whenever the devices are distinct and support
+ * multicast (TINYR_NVLS=0 disables it); otherwise "peer: <reason>": the peer-memory kernel.  Results are identical. */
+const char* tr_multi_exchange_kind(tr_multi* m);
+/* Benchmark hook: reps back-to-back exchanges on all devices at once; the slowest device's CUDA-event time / reps, in us. */
+int tr_multi_time_exchange(tr_multi* m, uint32_t reps, double* us_per_exchange);
 uint64_t tr_checksum_rgb8(const uint8_t* rgb8, size_t n_bytes);                  /* host twin of the device checksum */
 /* Deterministic light set for tr_scene_render_ao (host only): SplitMix64(seed) -> uniform sphere directions, computed
  * in double and rounded to f32, rejecting directions on which the reference's occlusion pipeline panics or reads

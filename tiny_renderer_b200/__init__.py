@@ -112,7 +112,7 @@ def lib():
             "tr_multi_create": [ctypes.POINTER(vp), ctypes.POINTER(_SceneDesc), vp, u32],
             "tr_multi_create_from_dir": [ctypes.POINTER(vp), ctypes.c_char_p, ctypes.c_char_p, u32, u32, vp, u32, u32],
             "tr_multi_set_camera": [vp, vp, vp, vp], "tr_multi_render_views": [vp, vp, u32, vp, vp],
-            "tr_multi_render_ao": [vp, vp, u32, vp],
+            "tr_multi_render_ao": [vp, vp, u32, vp], "tr_multi_time_exchange": [vp, u32, ctypes.POINTER(ctypes.c_double)],
             "tr_host_invalidate": [vp, ctypes.c_size_t], "tr_scene_transfer_stats": [vp, vp, i32],
             "tr_ao_generate_lights": [vp, u32, vp, vp, ctypes.c_uint64, u32, ctypes.c_float, vp, ctypes.POINTER(ctypes.c_uint64)],
         }
@@ -124,6 +124,7 @@ def lib():
         L.tr_multi_destroy.argtypes = [vp]; L.tr_multi_destroy.restype = None
         L.tr_multi_device_count.argtypes = [vp]; L.tr_multi_device_count.restype = ctypes.c_uint32
         L.tr_multi_scene.argtypes = [vp, u32]; L.tr_multi_scene.restype = vp
+        L.tr_multi_exchange_kind.argtypes = [vp]; L.tr_multi_exchange_kind.restype = ctypes.c_char_p
         L.tr_mesh_free.argtypes = [ctypes.POINTER(_Mesh)]; L.tr_mesh_free.restype = None
         L.tr_pixels_free.argtypes = [ctypes.POINTER(_Pixels)]; L.tr_pixels_free.restype = None
         L.tr_last_error.restype = ctypes.c_char_p

@@ -129,4 +129,35 @@ __global__ void __launch_bounds__(kPeerThreads, 1) k_ao_reduce_peers(const PeerA
     peer_barrier(a, a.value + 1u);
 }
 
+// K9n: the same sum through the NVSwitch (NVLS).  When the accumulators of all ranks are bound to one multicast object
+// (tinyr_multi.inc: one process, cuMulticast* + cuMemCreate instead of cudaMalloc), `multimem.ld_reduce` on the multicast
+// address returns the sum of the R copies formed INSIDE the switch, and `multimem.st` writes a value to all R copies:
+// rank r reads its slice once (one element in, instead of R - 1 peer loads) and writes it once (instead of R - 1 peer
+// stores), so per rank 1 / R of the buffer crosses its NVLink in each direction, whatever R is.  The integer multimem
+// operations are scalar; the u32 sums travel as packed u64 pairs — exact, because a 32-bit sum never carries (255 per
+// light and pixel: 16 M lights would be needed).  Same barriers as k_ao_reduce_peers (flags through the unicast mappings).
+__device__ __forceinline__ unsigned long long mm_ld_reduce_add_u64(const unsigned long long* mc) {
+    unsigned long long v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(v) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mm_st_u64(unsigned long long* mc, unsigned long long v) {
+    asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" :: "l"(mc), "l"(v) : "memory");
+}
+constexpr int kNvlsUnroll = 8;      // in-switch reductions in flight per thread
+__global__ void __launch_bounds__(kPeerThreads, 1) k_ao_reduce_nvls(const PeerArgs a, unsigned long long* mc) {
+    if (!peer_barrier(a, a.value)) return;
+    const unsigned long long n64 = 2ull * a.n_vec;
+    const unsigned long long lo = n64 * a.rank / a.world, hi = n64 * (a.rank + 1) / a.world;
+    const unsigned long long stride = (unsigned long long)kPeerBlocks * kPeerThreads;
+    for (unsigned long long i = lo + blockIdx.x * kPeerThreads + threadIdx.x; i < hi; i += stride * kNvlsUnroll) {
+        unsigned long long v[kNvlsUnroll];
+#pragma unroll
+        for (int k = 0; k < kNvlsUnroll; ++k) if (i + k * stride < hi) v[k] = mm_ld_reduce_add_u64(mc + i + k * stride);
+#pragma unroll
+        for (int k = 0; k < kNvlsUnroll; ++k) if (i + k * stride < hi) mm_st_u64(mc + i + k * stride, v[k]);
+    }
+    peer_barrier(a, a.value + 1u);
+}
+
 }  // namespace tr

@@ -78,6 +78,8 @@ struct tr_scene {
     // K9 (k_peer.cuh): the accumulators of all ranks, mapped through CUDA IPC by tr_scene_ao_open_peers
     uint32_t* peer_buf[kMaxPeers] = {};
     uint32_t peer_world = 0, peer_rank = 0, peer_value = 1;
+    unsigned long long* nvls_mc = nullptr;   // multicast mapping of all ranks' accumulators (tr_multi_*, NVLS): K9n instead of K9
+    bool ao_vmm = false;               // `ao` is a VMM mapping owned by a tr_multi (not cudaFree'd here)
     bool peer_ipc = true;              // peer_buf entries were opened from CUDA IPC handles (one process per GPU); false: plain peer pointers (tr_multi_*)
     int* peer_status = nullptr;        // mapped host word the kernel sets when a barrier times out
     AoList ao_list{};                  // covered pixels of the camera view (many-light AO batch), allocated on first use
@@ -390,6 +392,7 @@ void preload_peer_kernels() {
     cudaFuncGetAttributes(&fa, k_ao_reduce_peers<2>);
     cudaFuncGetAttributes(&fa, k_ao_reduce_peers<4>);
     cudaFuncGetAttributes(&fa, k_ao_reduce_peers<8>);
+    cudaFuncGetAttributes(&fa, k_ao_reduce_nvls);
     cudaGetLastError();
 }
 
@@ -424,7 +427,7 @@ void destroy_impl(tr_scene* s) {
         cudaFree(sl.cam.rec); cudaFree(sl.cam.var); cudaFree(sl.cam.bbox); cudaFree(sl.lit.rec); cudaFree(sl.lit.bbox);
         cudaFree(sl.bins.count); cudaFree(sl.bins.list);
     }
-    cudaFree(s->geom); cudaFree(s->tile_order); cudaFree(s->ao); cudaFree(s->ao_list.frag); cudaFree(s->ao_list.pix); cudaFree(s->ao_list.count); cudaFree(s->diag); cudaFree(s->host_stats); cudaFree(s->d_checksums); cudaFree(s->scratch);
+    cudaFree(s->geom); cudaFree(s->tile_order); if (!s->ao_vmm) cudaFree(s->ao); cudaFree(s->ao_list.frag); cudaFree(s->ao_list.pix); cudaFree(s->ao_list.count); cudaFree(s->diag); cudaFree(s->host_stats); cudaFree(s->d_checksums); cudaFree(s->scratch);
     if (s->own_stream) cudaStreamDestroy(s->own_stream);
     delete s;
 }

@@ -377,6 +377,16 @@ class MultiScene:
                                            frames_out.ctypes.data if frames_out is not None else None))
         return cs
 
+    def exchange_kind(self):
+        """"nvls" (in-switch multimem reduction) or "peer: <why not nvls>" (tr_multi_exchange_kind)."""
+        return lib().tr_multi_exchange_kind(self._h).decode()
+
+    def time_exchange(self, reps=5):
+        """us per exchange of the accumulators, slowest device (tr_multi_time_exchange); the sums are garbage afterwards."""
+        us = ctypes.c_double(0.0)
+        _check(lib().tr_multi_time_exchange(self._h, int(reps), ctypes.byref(us)))
+        return us.value
+
     def render_ao(self, light_dirs):
         lights = np.ascontiguousarray(light_dirs, np.float32).reshape(-1, 3)
         out = np.empty((self.height, self.width), np.uint32)
