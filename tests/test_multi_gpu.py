@@ -106,16 +106,26 @@ def test_native_multi_ao_equals_single_scene_and_oracle():
     o = oracle_lib.OracleScene(w, h, m, "occlusion")
     o.set_camera(lf, la, up)
     assert np.array_equal(want, o.render_ao(lights))
+    kinds = set()
     for devices in _device_lists():
-        g = MultiScene(w, h, m, "occlusion", devices, ring=2)
-        assert g.device_count() == len(devices)
-        g.set_camera(lf, la, up)
-        for rep in range(2):            # the barrier flags of the exchange kernel carry over from call to call
-            got = g.render_ao(lights)
-            assert np.array_equal(got, want), (devices, rep, int((got != want).sum()))
-        for i in range(len(devices)):   # every device's accumulator holds the total
-            assert np.array_equal(g.scene(i).read_ao(), want), (devices, i)
-        g.close()
+        # distinct devices on an NVSwitch box sum inside the switch (NVLS); TINYR_NVLS=0 keeps the peer-memory kernel
+        for nvls in (("1", "0") if len(set(devices)) == len(devices) > 1 else ("1",)):
+            os.environ["TINYR_NVLS"] = nvls
+            g = MultiScene(w, h, m, "occlusion", devices, ring=2)
+            assert g.device_count() == len(devices)
+            g.set_camera(lf, la, up)
+            kind = g.exchange_kind()
+            assert kind == "nvls" or kind.startswith("peer: "), kind
+            assert not (nvls == "0" and kind == "nvls")
+            kinds.add(kind.split(":")[0])
+            for rep in range(2):            # the barrier flags of the exchange kernel carry over from call to call
+                got = g.render_ao(lights)
+                assert np.array_equal(got, want), (devices, kind, rep, int((got != want).sum()))
+            for i in range(len(devices)):   # every device's accumulator holds the total
+                assert np.array_equal(g.scene(i).read_ao(), want), (devices, kind, i)
+            g.close()
+    os.environ.pop("TINYR_NVLS", None)
+    assert "peer" in kinds
     one.close()
 
 
