@@ -160,8 +160,9 @@ int tr_multi_set_camera(tr_multi* m, const float look_from[3], const float look_
 int tr_multi_render_views(tr_multi* m, const tr_view* views, uint32_t n_views, uint64_t* checksums, uint8_t* frames_rgb8_topdown);
 int tr_multi_render_ao(tr_multi* m, const float* light_dirs_xyz, uint32_t n_lights, uint32_t* accum_host);
 /* "nvls": the accumulators live in memory bound to one NVSwitch multicast object and are summed INSIDE the switch
- * (multimem.ld_reduce / multimem.st, k_peer.cuh k_ao_reduce_nvls) — used whenever the devices are distinct and support
- * multicast (TINYR_NVLS=0 disables it); otherwise "peer: <reason>": the peer-memory kernel.  Results are identical. */
+ * (multimem.ld_reduce / multimem.st, k_peer.cuh k_ao_reduce_nvls) — only with TINYR_NVLS=1 in the environment, distinct
+ * devices and multicast support; otherwise "peer: <reason>": the peer-memory kernel, which is the default because it is
+ * the faster of the two at 2, 4 and 8 B200s (profiles/r2_probes.md).  Results are identical. */
 const char* tr_multi_exchange_kind(tr_multi* m);
 /* Benchmark hook: reps back-to-back exchanges on all devices at once; the slowest device's CUDA-event time / reps, in us. */
 int tr_multi_time_exchange(tr_multi* m, uint32_t reps, double* us_per_exchange);

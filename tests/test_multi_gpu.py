@@ -108,15 +108,17 @@ def test_native_multi_ao_equals_single_scene_and_oracle():
     assert np.array_equal(want, o.render_ao(lights))
     kinds = set()
     for devices in _device_lists():
-        # distinct devices on an NVSwitch box sum inside the switch (NVLS); TINYR_NVLS=0 keeps the peer-memory kernel
-        for nvls in (("1", "0") if len(set(devices)) == len(devices) > 1 else ("1",)):
-            os.environ["TINYR_NVLS"] = nvls
+        # default = the peer-memory kernel (the faster one); TINYR_NVLS=1 sums inside the NVSwitch where the box can
+        for nvls in ((None, "1") if len(set(devices)) == len(devices) > 1 else (None,)):
+            os.environ.pop("TINYR_NVLS", None)
+            if nvls:
+                os.environ["TINYR_NVLS"] = nvls
             g = MultiScene(w, h, m, "occlusion", devices, ring=2)
             assert g.device_count() == len(devices)
             g.set_camera(lf, la, up)
             kind = g.exchange_kind()
             assert kind == "nvls" or kind.startswith("peer: "), kind
-            assert not (nvls == "0" and kind == "nvls")
+            assert not (nvls is None and kind == "nvls")
             kinds.add(kind.split(":")[0])
             for rep in range(2):            # the barrier flags of the exchange kernel carry over from call to call
                 got = g.render_ao(lights)

@@ -1,7 +1,7 @@
 """AO exchange of the native multi-GPU driver (tr_multi_*), one process over G devices: result against a single scene, which
 exchange runs ("nvls" = multimem reductions inside the NVSwitch, or the peer-memory kernel) and how long one exchange of
 the 33 MB of 4K sums takes (tr_multi_time_exchange: 20 back to back, slowest device, CUDA events).
-    python tools/nvls_check.py [G];   TINYR_NVLS=0 python tools/nvls_check.py [G]        (run under gpurun --gpus G)"""
+    TINYR_NVLS=1 python tools/nvls_check.py [G];   python tools/nvls_check.py [G]        (run under gpurun --gpus G)"""
 import json
 import os
 import sys
