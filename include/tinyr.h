@@ -167,6 +167,15 @@ const char* tr_multi_exchange_kind(tr_multi* m);
 /* Benchmark hook: reps back-to-back exchanges on all devices at once; the slowest device's CUDA-event time / reps, in us. */
 int tr_multi_time_exchange(tr_multi* m, uint32_t reps, double* us_per_exchange);
 uint64_t tr_checksum_rgb8(const uint8_t* rgb8, size_t n_bytes);                  /* host twin of the device checksum */
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).  The device checksum (K8, the one
+ * tr_scene_render_views returns per view) of a caller's frame `rgb8` (host or any UVA pointer) on `device`, with ALL device
+ * scratch — the accumulator and the device copy of the frame — in a file-scope static __device__ array
+ * (csrc/tinyr_static.cu) that every GPU using this entry point holds until the process exits.  Allocates nothing.
+ * n_bytes > TR_STATIC_CHECKSUM_MAX_BYTES -> TR_ERR_INVALID_ARGUMENT.  Synchronous (legacy default stream).  Every call
+ * on a device shares the array: calls that overlap on the GPU would race; inside one process a mutex prevents that. */
+#define TR_STATIC_CHECKSUM_MAX_BYTES (8u << 20)   /* 8 MiB: a 1920x1080 RGB8 frame is 6,220,800 bytes */
+int tr_checksum_rgb8_static(int device, const uint8_t* rgb8, size_t n_bytes, uint64_t* checksum);
 /* Deterministic light set for tr_scene_render_ao (host only): SplitMix64(seed) -> uniform sphere directions, computed
  * in double and rounded to f32, rejecting directions on which the reference's occlusion pipeline panics or reads
  * its shadow buffer on the wrong row: light parallel to `up` (shader.rs:194), light == -z (shader.rs:921), any model

@@ -130,6 +130,8 @@ def lib():
         L.tr_last_error.restype = ctypes.c_char_p
         L.tr_version.restype = ctypes.c_char_p
         L.tr_checksum_rgb8.argtypes = [vp, ctypes.c_size_t]; L.tr_checksum_rgb8.restype = ctypes.c_uint64
+        L.tr_checksum_rgb8_static.argtypes = [ctypes.c_int, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_uint64)]
+        L.tr_checksum_rgb8_static.restype = ctypes.c_int
         L.tr_host_alloc.argtypes = [ctypes.c_size_t]; L.tr_host_alloc.restype = vp
         L.tr_host_free.argtypes = [vp]; L.tr_host_free.restype = None
         _LIB = L
@@ -145,5 +147,5 @@ def _f3(v):
     return np.ascontiguousarray(np.asarray(v, dtype=np.float32).reshape(3))
 
 
-from .scene import (Scene, Model, load_obj, load_tga, write_tga, load_model_dir, checksum_rgb8, device_count, pinned_empty,  # noqa: E402,F401
+from .scene import (Scene, Model, load_obj, load_tga, write_tga, load_model_dir, checksum_rgb8, checksum_rgb8_static, device_count, pinned_empty,  # noqa: E402,F401
                     generate_ao_lights, AO_LIGHT_SEED, AO_NDC_MARGIN, bench_atomic_min, host_invalidate)

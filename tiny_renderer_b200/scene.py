@@ -74,6 +74,18 @@ def checksum_rgb8(img):
     return int(lib().tr_checksum_rgb8(a.ctypes.data, a.size))
 
 
+STATIC_CHECKSUM_MAX_BYTES = 8 << 20     # TR_STATIC_CHECKSUM_MAX_BYTES (include/tinyr.h)
+
+
+def checksum_rgb8_static(img, device=0):
+    """tr_checksum_rgb8_static: the device checksum of a host frame with its scratch in a static device array (no
+    allocation on the device; at most STATIC_CHECKSUM_MAX_BYTES per call)."""
+    a = np.ascontiguousarray(img, np.uint8)
+    out = ctypes.c_uint64(0)
+    _check(lib().tr_checksum_rgb8_static(int(device), a.ctypes.data, a.size, ctypes.byref(out)))
+    return int(out.value)
+
+
 AO_LIGHT_SEED = 0x5EED0A0      # SURVEY.md §8(d) config 4
 AO_NDC_MARGIN = 0.97
 
