@@ -340,22 +340,22 @@ def raster_kernel(pipe, threads):
 
 def setup_kernel(pipe):
     """The vertex set-up kernel: one instantiation for the camera pass of every pipeline, one for the light pass."""
-    return "k_vertex_setup<true>" if pipe == "light_depth" else "k_vertex_setup<false>"
+    return "k_vertex_setup<true,false>" if pipe == "light_depth" else "k_vertex_setup<false,false>"     # <LIGHT_PASS, SORT> (k_setup.cuh)
 
 
 def ncu_kernel_summary(want):
     """Entry of the kernel whose name contains `want` (DRAM bytes, duration and warp instructions per launch).  Also finds
     captures taken before the kernels were templated on pipeline structs (r1: k_raster<4,128>, k_vertex_setup<0>)."""
     def norm(name):     # ncu spells "k_raster<tr::PipelineDarboux, 128>" / "k_raster<(int)4, (int)128>"
-        return name.replace("(int)", "").replace("tr::", "").replace(" ", "")
+        return name.replace("(int)", "").replace("(bool)", "").replace("tr::", "").replace(" ", "")
     wants = [want.replace(" ", "")]
     for pipe, st in PIPE_STRUCT.items():
         if st in want:
             wants.append(wants[0].replace("k_raster<" + st, "k_raster<%d" % LEGACY_ID[pipe]))
-    if wants[0] == "k_vertex_setup<false>":     # earlier spellings of the same kernel in committed captures
-        wants += ["k_vertex_setup<0>", "k_vertex_setup<PipelineDarboux>", "k_vertex_setup<PipelinePhong>"]
-    if wants[0] == "k_vertex_setup<true>":
-        wants += ["k_vertex_setup<1>", "k_vertex_setup<PassLightDepth>"]
+    if wants[0] == "k_vertex_setup<false,false>":     # earlier spellings of the same kernel in committed captures
+        wants += ["k_vertex_setup<0,0>", "k_vertex_setup<false>", "k_vertex_setup<0>", "k_vertex_setup<PipelineDarboux>", "k_vertex_setup<PipelinePhong>"]
+    if wants[0] == "k_vertex_setup<true,false>":
+        wants += ["k_vertex_setup<1,0>", "k_vertex_setup<true>", "k_vertex_setup<1>", "k_vertex_setup<PassLightDepth>"]
     table, src = ncu_summaries()
     for w in wants:
         for k, v in table.items():

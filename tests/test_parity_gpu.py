@@ -439,3 +439,26 @@ def test_hundreds_of_renders_without_clear(tinyr, oracle):
             st = parity.compare(g, o, rgb_frac=1.0)
             assert st["depth_bits_differ"] == 0 and st["rgb_exact_frac"] == 1.0, (i, st)
     g.close()
+
+
+@pytest.mark.parametrize("pipeline", ["darboux", "shadow"])
+def test_lone_4k_frames_in_a_row_launch_order_follows_the_previous_frame(tinyr, oracle, pipeline):
+    """Lone frames walk the tiles in the order of what they cost in the previous lone frame (k_setup.cuh sort_tiles,
+    k_raster.cuh tile_cursor / tile_cost): the order must stay a permutation of all tiles whatever the previous view was,
+    so every frame of a sequence with very different views equals the oracle's, bit for bit."""
+    from tiny_renderer_b200.scene import Scene
+    model = get_model("diablo")
+    w, h = 3840, 2160
+    g = Scene(w, h, model, pipeline)
+    o = oracle.OracleScene(w, h, model, pipeline)
+    two = pipeline in TWO_PASS
+    for step, (cam, light) in enumerate([(0.4, 0.7), (0.4, 0.7), (3.3, 2.1), (1.9, 0.2)]):
+        lf, la, up, l = assets.view_vectors(cam, light)
+        if step == 2:       # a very different frame in between (camera turned away: the model projects mirrored, no clipping)
+            away = (lf[0] * 3.0, lf[1] * 3.0, lf[2] * 3.0)
+            parity.drive(g, lf, away, up, l)
+        parity.drive(g, lf, la, up, l)
+        parity.drive(o, lf, la, up, l)
+        st = parity.compare(g, o, two_pass=two)
+        assert st["rgb_exact_frac"] == 1.0 and st["depth_bits_differ"] == 0, (step, st)
+    g.close()

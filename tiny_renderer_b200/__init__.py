@@ -13,7 +13,7 @@ import numpy as np
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_PKG, "csrc")
-LIB_PATH = os.path.join(_PKG, "libtinyr.so")
+LIB_PATH = os.environ.get("TINYR_LIB") or os.path.join(_PKG, "libtinyr.so")     # (TINYR_LIB: another build of the same ABI, for A/B runs)
 CLI_PATH = os.path.join(_PKG, "tiny_renderer")
 NO_TRIANGLE = 0xFFFFFFFF
 PIPELINES = ("default", "phong", "normal_map", "specular", "darboux", "shadow", "occlusion")

@@ -86,6 +86,12 @@ struct RasterArgs {
     float* depth;              // depth-only mode (shadow buffer)
     uint32_t* depth_clear;     // depth-only mode, per tile: nonzero = every depth of the tile holds the cleared value already
     unsigned long long* diag;
+    uint32_t n_tiles;
+    // Lone-frame launches: per tile (under its position in the static centre-out order), the SM cycles this launch spent on it.  The vertex
+    // set-up kernel of the NEXT lone frame sorts the launch order by it, longest first (k_setup.cuh: sort_tiles).  Non-null
+    // also means that tile_order was written by the set-up kernel in front of this launch, i.e. is read after the wait.
+    uint32_t* tile_cost;
+    const uint32_t* tile_rank; // tile index -> its position in the static centre-out order (the index tile_cost is kept under)
 };
 
 // The tile is cut into kBlocksX x kBlocksY blocks of 8 x kBlockH pixels (one warp pass each); bit (by * kBlocksX + bx)
@@ -166,6 +172,21 @@ __device__ __forceinline__ void stage_polygon(uint32_t t, int4 bb, float4 r0, fl
     s_maskx[slot] = exact ? 0u : blocks;
 }
 
+#ifdef TR_TIMELINE
+// Diagnostic build only (make EXTRA=-DTR_TIMELINE, tools/lone_timeline.py): per CTA of the last k_raster launch, words
+// [0] entry, [1] past griddepcontrol.wait, [2] first filter round done, [3] exit (globaltimer, ns), [4] SM id,
+// [5] staged polygons of the first round.  Read back with tr_debug_timeline (tinyr.cu, same macro).
+constexpr int kTimelineWords = 8, kTimelineCtas = 8192;
+__device__ unsigned long long g_timeline[kTimelineCtas * kTimelineWords];
+__device__ __forceinline__ unsigned long long timeline_now() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ void timeline_mark(uint32_t pos, int word, unsigned long long v) {
+    if (threadIdx.x == 0 && pos < (uint32_t)kTimelineCtas) g_timeline[pos * kTimelineWords + word] = v;
+}
+#define TR_TIMELINE_MARK(pos, word, v) timeline_mark(pos, word, v)
+#else
+#define TR_TIMELINE_MARK(pos, word, v) ((void)0)
+#endif
+
 // Winner state of a lane's pixels as left in memory by earlier work on the target (a render without clear, or an
 // earlier round of a long polygon list).  Out of line on purpose: inlined, the compiler predicates these loads and
 // conversions into every block's start-up, where a cleared frame — the common case — never needs them.
@@ -218,6 +239,9 @@ __device__ __forceinline__ void raster_tile(const RasterArgs& a, const ShadeArgs
     // Everything above only reads launch-time constants (the tile order table is written at scene creation); from here
     // on the kernel reads what the vertex set-up kernel in front of it wrote (tinyr.cu: launch_raster).
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    TR_TIMELINE_MARK(launch_pos, 1, timeline_now());
+    TR_TIMELINE_MARK(launch_pos, 2, 0ull);
+    TR_TIMELINE_MARK(launch_pos, 5, 0ull);
     const uint32_t n_bin = a.bins.count[a.bins.parity * a.bins.n_cells + cell];
     // The filter below is a chain of dependent loads (bin count -> list entry -> bounding box -> setup record) that
     // the whole CTA waits for.  The first list entry of every thread is fetched alongside the count (the slot exists
@@ -283,6 +307,9 @@ __device__ __forceinline__ void raster_tile(const RasterArgs& a, const ShadeArgs
         __syncthreads();
         const int n_list = min(s_count, kCap);
         const int n_inexact = s_inexact;
+#ifdef TR_TIMELINE
+        if (!touched) { TR_TIMELINE_MARK(launch_pos, 2, timeline_now()); TR_TIMELINE_MARK(launch_pos, 5, (unsigned long long)n_list); }
+#endif
         scan_from = (uint32_t)s_next;       // == n_src when everything was staged
         more = scan_from < n_src;
         // A round that staged nothing reached the end of the source list (more is false).  In the shading modes it still
@@ -504,10 +531,31 @@ __device__ __forceinline__ void raster_tile(const RasterArgs& a, const ShadeArgs
     }
 }
 
+// One launch = one frame, one CTA per tile.  The lone shape also records what each tile cost (tile_cost), from which the
+// set-up kernel of the next lone frame sorts the launch order.  (A form that launched only as many CTAs as are resident
+// and let each walk the order through a device counter was measured with it: 1 us slower per 4K frame than this one
+// with the sorted order, no faster without — profiles/r2_probes.md — and removed.)
 template <class PIPE, int THREADS>
 __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u, const __grid_constant__ CUtensorMap rgb_map,
                                          const __grid_constant__ CUtensorMap rgb_map_top) {
+    constexpr bool LONE = THREADS == kRasterThreads;
+    __shared__ uint32_t s_t0;          // (shared, not a register: the tile code's register budget is exhausted)
+    if (LONE && a.tile_cost != nullptr) {
+        asm volatile("griddepcontrol.wait;" ::: "memory");     // the launch order is the set-up kernel's output
+        if (threadIdx.x == 0) s_t0 = (uint32_t)clock();
+    }
+    TR_TIMELINE_MARK(blockIdx.x, 0, timeline_now());
     raster_tile<PIPE, THREADS>(a, sa, u, &rgb_map, &rgb_map_top, blockIdx.x);
+#ifdef TR_TIMELINE
+    unsigned sm;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+    TR_TIMELINE_MARK(blockIdx.x, 3, timeline_now());
+    TR_TIMELINE_MARK(blockIdx.x, 4, (unsigned long long)sm);
+#endif
+    if (LONE && a.tile_cost != nullptr && threadIdx.x == 0) {
+        const uint32_t xy = __ldg(&a.tile_order[blockIdx.x]);
+        a.tile_cost[__ldg(&a.tile_rank[(xy >> 16) * a.tiles_x + (xy & 0xffffu)])] = (uint32_t)clock() - s_t0;
+    }
 }
 
 // Several views in ONE launch (multi-view-per-launch batching at small resolutions): blockIdx.y

@@ -11,11 +11,85 @@ namespace tr {
 //   [0..8]  p0 p1 p2 (xyz)   [9..14] u0 u1 u2 v0' v1' v2' with v' = 1 - v   [15..23] n0 n1 n2 (xyz)
 constexpr int kStaticWords = 24;
 
+// Launch order of the NEXT tile kernel, longest tile first (lone frames only; null cost = off).  A lone 4K frame spends a
+// third of its tile kernel in a tail of late-started heavy tiles (per-CTA timeline: tools/lone_timeline.py); launching
+// the tiles in the order of what they cost in the previous lone frame — views change little from frame to frame — cuts
+// a darboux frame's tile kernel from 57 to 46 us and a phong frame's from 36 to 27 (tools/lone_order_probe.py).
+struct TileSort {
+    const uint32_t* cost;     // per centre-out position: SM cycles of that tile in the previous lone launch of this pass (k_raster.cuh)
+    const uint32_t* base;     // n_tiles launch positions -> y << 16 | x, centre-out (ties keep this order)
+    uint32_t* order;          // out: n_tiles entries, a permutation of base
+    uint32_t n_tiles;
+};
+constexpr int kSortBuckets = 16, kSortShift = 13;        // 8,192 cycles (4.2 us) per bucket: as good as an exact sort (probe)
+constexpr int kSortMaxTiles = 16384;                     // one byte of shared memory per tile (8K: 16,200 tiles)
+static_assert(kSortBuckets * 4 == 64, "the prefix below handles two entries per lane of one warp");
+
+// One CTA of the set-up kernel (its last block, 128 threads): counting sort of the centre-out positions by cost bucket,
+// longest first.  It has to finish inside the ~6 us the other blocks take, so nothing in it is a chain of dependent
+// memory operations: costs and table entries are fetched at once (32 + 32 coalesced loads in flight per thread), counted
+// and placed with shared-memory atomics.  Warp w owns the w-th quarter of the centre-out order and writes its members of a bucket behind
+// those of warp w - 1, so a bucket keeps the centre-out order up to the order inside one warp's quarter — which only
+// matters to speed, never to the image: every position is written exactly once (the output is a permutation of base).
+__device__ __forceinline__ uint32_t sort_bucket(uint32_t cycles) {        // bucket 0 = longest
+    return (uint32_t)(kSortBuckets - 1) - min((uint32_t)(kSortBuckets - 1), cycles >> kSortShift);
+}
+__device__ __forceinline__ void sort_tiles(const TileSort& q) {
+    __shared__ uint8_t s_bucket[kSortMaxTiles];
+    __shared__ uint32_t s_run[kSortBuckets * 4];         // entry b * 4 + w: warp w's count of bucket b, then its next output slot
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t n = q.n_tiles;
+    const uint32_t per = ((n + 3u) / 4u + 31u) & ~31u;   // positions per warp
+    const uint32_t w0 = min(n, (uint32_t)warp * per), w1 = min(n, w0 + per);
+    // the table entries this lane will place first: in flight while the costs are fetched and counted
+    uint32_t xy[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) { const uint32_t p = w0 + 32u * j + lane; xy[j] = p < w1 ? __ldg(&q.base[p]) : 0u; }
+    if (tid < kSortBuckets * 4) s_run[tid] = 0u;
+    __syncthreads();
+    for (uint32_t r0 = 0; r0 < n; r0 += 4096u) {
+        uint32_t c[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { const uint32_t p = r0 + 128u * j + tid; c[j] = p < n ? q.cost[p] : 0u; }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const uint32_t p = r0 + 128u * j + tid;
+            if (p < n) {
+                const uint32_t b = sort_bucket(c[j]), owner = (p >= per ? 1u : 0u) + (p >= 2u * per ? 1u : 0u) + (p >= 3u * per ? 1u : 0u);
+                s_bucket[p] = (uint8_t)b;
+                atomicAdd(&s_run[b * 4 + owner], 1u);
+            }
+        }
+    }
+    __syncthreads();
+    if (warp == 0) {            // exclusive prefix over the 64 counts in (bucket, warp) order, two entries per lane
+        const uint32_t a = s_run[2 * lane], b = s_run[2 * lane + 1];
+        uint32_t incl = a + b;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+        s_run[2 * lane] = incl - a - b;
+        s_run[2 * lane + 1] = incl - b;
+    }
+    __syncthreads();
+    for (uint32_t i0 = w0; i0 < w1; i0 += 1024u) {
+        if (i0 != w0) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) { const uint32_t p = i0 + 32u * j + lane; xy[j] = p < w1 ? __ldg(&q.base[p]) : 0u; }
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const uint32_t p = i0 + 32u * j + lane;
+            if (p < w1) q.order[atomicAdd(&s_run[s_bucket[p] * 4 + warp], 1u)] = xy[j];
+        }
+    }
+}
+
 struct SetupOut {
     float4* rec;      // n_triangles x 4 float4 (kRecWords)
     float4* var;      // n_triangles x 6 float4 (kVarWords), may be null when the pipeline needs none
     int4* bbox;       // n_triangles: xmin ymin xmax ymax clamped to the screen; xmin > xmax when not drawn
     Bins bins;        // K2: per-cell polygon lists for the raster kernel that follows
+    TileSort sort;    // cost != null: the grid has one extra block that writes the tile kernel's launch order
 };
 
 // LIGHT_PASS: shadow/occlusion pass 1 — no culling, transform by u.shadow, no varyings.  Otherwise `pipeline` selects the
@@ -24,12 +98,19 @@ struct SetupOut {
 // was measured in r2 (smaller kernels, 792-1,552 instructions instead of 2,080) and cost the phong + darboux view batch
 // 5 % (266 vs 279 Gpx/s; each pipeline alone unchanged) — two scenes with different pipelines then keep two set-up
 // kernels resident beside their tile kernels, and the SMs' 32 KB L1.5 instruction cache is already oversubscribed.
-template <bool LIGHT_PASS>
+template <bool LIGHT_PASS, bool SORT = false>
 __device__ __forceinline__ void vertex_setup(const float4* __restrict__ geom, const SetupOut& out, const Uniforms& u, int pipeline,
                                              unsigned long long* diag) {
     // The tile kernel behind this one is launched with programmatic stream serialization (tinyr.cu: launch_raster): let
     // it start now; it waits for this grid's completion before it touches anything written here.
     asm volatile("griddepcontrol.launch_dependents;");
+    if (SORT && out.sort.cost != nullptr && blockIdx.x == gridDim.x - 1) {
+        // the extra block: its share of the counter zeroing below, then the launch order
+        uint32_t* other = out.bins.count + (out.bins.parity ^ 1u) * out.bins.n_cells;
+        for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < out.bins.n_cells; c += gridDim.x * blockDim.x) other[c] = 0u;
+        sort_tiles(out.sort);
+        return;
+    }
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = t < u.n_triangles;        // no early return: the whole warp takes part in the binning
     if (!valid) t = u.n_triangles - 1;
@@ -142,10 +223,12 @@ __device__ __forceinline__ void vertex_setup(const float4* __restrict__ geom, co
     }
 }
 
-template <bool LIGHT_PASS>
+// SORT: the lone-frame form, whose last block writes the tile kernel's launch order (sort_tiles; 25 KB of shared memory
+// that the batch form, resident beside other frames' tile kernels, does not carry).
+template <bool LIGHT_PASS, bool SORT = false>
 __global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__ geom, const SetupOut out, const Uniforms u, int pipeline,
                                                      unsigned long long* diag) {
-    vertex_setup<LIGHT_PASS>(geom, out, u, pipeline, diag);
+    vertex_setup<LIGHT_PASS, SORT>(geom, out, u, pipeline, diag);
 }
 
 // Several views in one launch (see k_raster_views): blockIdx.y selects the view's uniforms and frame slot.

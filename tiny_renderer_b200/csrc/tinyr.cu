@@ -72,6 +72,12 @@ struct tr_scene {
     // launch position -> tile coordinates (y << 16 | x), two orders of n_tiles entries each: [0] tiles sorted by
     // distance from the screen centre, [1] plain row order
     uint32_t* tile_order = nullptr;
+    // lone frames: per pass (0 light depth, 1 camera) the tiles' cost in the last lone launch and the launch order the
+    // set-up kernel sorts from it (k_setup.cuh: sort_tiles); order_sorted[p]: the set-up kernel in front wrote order p
+    uint32_t* tile_cost = nullptr;       // [pass][centre-out position]
+    uint32_t* tile_rank = nullptr;       // tile index -> centre-out position
+    uint32_t* tile_order_sorted = nullptr;
+    bool order_sorted[2] = {false, false};
     bool overlapping = false;            // a batch is running frames / light passes concurrently on the slot streams
     uint32_t debug_flags = 0;            // tr_scene_set_debug_flags -> Uniforms::debug_flags
     uint32_t* ao = nullptr;            // n_px sums, zero padding to a multiple of 4, then the kPeerFlagWords barrier flags of K9
@@ -335,8 +341,28 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
             packed[i] = ((order[i] / s->tiles_x) << 16) | (order[i] % s->tiles_x);
             packed[n_tiles + i] = ((uint32_t)(i / s->tiles_x) << 16) | (uint32_t)(i % s->tiles_x);
         }
+#ifdef TR_TIMELINE
+        // Diagnostic build only: TINYR_ORDER_PERM = file of n_tiles u32, entry i = the centre-out position that launches i-th
+        // (tools/lone_timeline.py: what a cost-sorted launch order would buy).
+        if (const char* f = getenv("TINYR_ORDER_PERM")) {
+            std::vector<uint32_t> perm(n_tiles), was(packed.begin(), packed.begin() + n_tiles);
+            FILE* fp = fopen(f, "rb");
+            if (fp && fread(perm.data(), 4, n_tiles, fp) == n_tiles)
+                for (size_t i = 0; i < n_tiles; ++i) packed[i] = was[perm[i] % n_tiles];
+            if (fp) fclose(fp);
+        }
+#endif
         CU(cudaMalloc(&s->tile_order, packed.size() * 4));
         CU(cudaMemcpy(s->tile_order, packed.data(), packed.size() * 4, cudaMemcpyHostToDevice));
+        std::vector<uint32_t> rank(n_tiles);
+        for (size_t i = 0; i < n_tiles; ++i) rank[order[i]] = (uint32_t)i;
+        CU(cudaMalloc(&s->tile_rank, n_tiles * 4));
+        CU(cudaMemcpy(s->tile_rank, rank.data(), n_tiles * 4, cudaMemcpyHostToDevice));
+        CU(cudaMalloc(&s->tile_cost, 2 * n_tiles * 4));
+        CU(cudaMemset(s->tile_cost, 0, 2 * n_tiles * 4));
+        CU(cudaMalloc(&s->tile_order_sorted, 2 * n_tiles * 4));
+        CU(cudaMemcpy(s->tile_order_sorted, packed.data(), n_tiles * 4, cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(s->tile_order_sorted + n_tiles, packed.data(), n_tiles * 4, cudaMemcpyHostToDevice));
     }
     s->slots.assign(s->ring, tr_scene::Slot{});
     for (uint32_t r = 0; r < s->ring; ++r) {
@@ -427,12 +453,17 @@ void destroy_impl(tr_scene* s) {
         cudaFree(sl.cam.rec); cudaFree(sl.cam.var); cudaFree(sl.cam.bbox); cudaFree(sl.lit.rec); cudaFree(sl.lit.bbox);
         cudaFree(sl.bins.count); cudaFree(sl.bins.list);
     }
-    cudaFree(s->geom); cudaFree(s->tile_order); if (!s->ao_vmm) cudaFree(s->ao); cudaFree(s->ao_list.frag); cudaFree(s->ao_list.pix); cudaFree(s->ao_list.count); cudaFree(s->diag); cudaFree(s->host_stats); cudaFree(s->d_checksums); cudaFree(s->scratch);
+    cudaFree(s->geom); cudaFree(s->tile_order); cudaFree(s->tile_cost); cudaFree(s->tile_rank); cudaFree(s->tile_order_sorted); if (!s->ao_vmm) cudaFree(s->ao); cudaFree(s->ao_list.frag); cudaFree(s->ao_list.pix); cudaFree(s->ao_list.count); cudaFree(s->diag); cudaFree(s->host_stats); cudaFree(s->d_checksums); cudaFree(s->scratch);
     if (s->own_stream) cudaStreamDestroy(s->own_stream);
     delete s;
 }
 
 // ---- pass issue ------------------------------------------------------------------------------------------
+
+// A lone frame (not part of an overlapped batch) runs the 256-thread tile kernel (k_raster.cuh); debug bit 1 forces the
+// batch shape.  TINYR_LONE_SORT=0: lone frames keep the static centre-out launch order (A/B in profiles/r2_probes.md).
+static const bool g_lone_sort = !(getenv("TINYR_LONE_SORT") && atoi(getenv("TINYR_LONE_SORT")) == 0);
+bool lone_shape(const tr_scene* s) { return !s->overlapping && (s->debug_flags & 2u) == 0u; }
 
 int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     if (s->n_tri == 0) return TR_OK;
@@ -442,6 +473,23 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     S(s).cam.bins = S(s).bins;
     S(s).lit.bins = S(s).bins;
     // (the vertex roles of all pipelines live in one kernel: k_setup.cuh)
+    const int pass = light_pass ? 0 : 1;
+    const uint32_t n_tiles = s->tiles_x * s->tiles_y;
+    s->order_sorted[pass] = false;
+    // (frames of fewer tiles than the device holds CTAs at once — 800x800: 325 — run as one wave, whatever the order)
+    if (lone_shape(s) && g_lone_sort && n_tiles > 1024u && n_tiles <= (uint32_t)kSortMaxTiles) {
+        // a lone frame: one more block sorts the tile kernel's launch order by the tiles' cost in the previous lone frame
+        SetupOut out = light_pass ? S(s).lit : S(s).cam;
+        out.sort.cost = s->tile_cost + (size_t)pass * n_tiles;
+        out.sort.base = s->tile_order;
+        out.sort.order = s->tile_order_sorted + (size_t)pass * n_tiles;
+        out.sort.n_tiles = n_tiles;
+        grid.x += 1;
+        if (light_pass) k_vertex_setup<true, true><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->pipeline, s->diag);
+        else k_vertex_setup<false, true><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->pipeline, s->diag);
+        s->order_sorted[pass] = true;
+        return launch_ok("k_vertex_setup");
+    }
     if (light_pass) k_vertex_setup<true><<<grid, 128, 0, s->stream>>>(s->geom, S(s).lit, u, s->pipeline, s->diag);
     else k_vertex_setup<false><<<grid, 128, 0, s->stream>>>(s->geom, S(s).cam, u, s->pipeline, s->diag);
     return launch_ok("k_vertex_setup");
@@ -502,6 +550,7 @@ RasterArgs raster_args(tr_scene* s, bool depth_only, uint32_t epoch, bool fresh,
     a.epoch = epoch; a.fresh = fresh ? 1 : 0;
     a.keys = S(s).keys; a.tile_state = S(s).tile_state; a.depth = S(s).shadow; a.depth_clear = S(s).shadow_clear; a.diag = s->diag;
     a.tile_order = s->tile_order + (row_order ? (size_t)s->tiles_x * s->tiles_y : 0);
+    a.n_tiles = s->tiles_x * s->tiles_y;
     return a;
 }
 
@@ -557,7 +606,14 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     dim3 grid(s->tiles_x * s->tiles_y);
     Scoped sp(s, depth_only ? KS_SHADOW : KS_RASTER);
     // CTA shape: 256 threads for a lone frame, 128 for overlapped batches (k_raster.cuh)
-    const int shape = (s->overlapping || (s->debug_flags & 2u) != 0u) ? 1 : 0;      // (debug bit 1: time the batch shape on a lone frame)
+    const int shape = lone_shape(s) ? 0 : 1;      // (debug bit 1: time the batch shape on a lone frame)
+    const int pass = depth_only ? 0 : 1;
+    if (shape == 0 && s->order_sorted[pass]) {
+        a.tile_order = s->tile_order_sorted + (size_t)pass * a.n_tiles;
+        a.tile_cost = s->tile_cost + (size_t)pass * a.n_tiles;
+        a.tile_rank = s->tile_rank;
+    }
+    s->order_sorted[pass] = false;
     if (mode == kModeDepthOnly) kRasterLightDepth[shape](s, grid, a, sa, u);
     else if (mode == kModeVisibility) kRasterVisibility[shape](s, grid, a, sa, u);
     else kPipelines[mode].raster[shape](s, grid, a, sa, u);
@@ -839,3 +895,14 @@ int tr_scene_device_frame(tr_scene* s, void** p) {
 
 #include "tinyr_batch.inc"
 #include "tinyr_multi.inc"
+
+#ifdef TR_TIMELINE
+// Diagnostic build only (see k_raster.cuh): copies the per-CTA timeline of the last tile-kernel launch on the current device.
+extern "C" int tr_debug_timeline(uint64_t* out, uint32_t n_ctas) {
+    using namespace tr;
+    if (!out || n_ctas > (uint32_t)kTimelineCtas) return fail(TR_ERR_INVALID_ARGUMENT, "tr_debug_timeline: bad argument");
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpyFromSymbol(out, g_timeline, (size_t)n_ctas * kTimelineWords * 8));
+    return TR_OK;
+}
+#endif
