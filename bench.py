@@ -397,6 +397,24 @@ def lone_frame_us(scene, views, reps=2):
     return {k: (t / n * 1e3) for k, (t, n) in kt.items() if n and t > 0}
 
 
+def settled_frame_us(scene, views, warm=3, frames=2):
+    """As lone_frame_us, for a view that has settled: every view is rendered `warm` times unprofiled, then `frames` times
+    profiled.  This is the reference's app loop (app.rs:166-247 re-renders continuously and turns the camera by
+    3 rad/s x frame time, i.e. < 0.1 degree per frame), and the case in which a lone frame launches its tiles in the order
+    of their cost in the previous frame (k_setup.cuh sort_tiles)."""
+    scene.kernel_times()
+    for v in views:
+        for i in range(warm + frames):
+            if i == warm:
+                scene.synchronize()
+                scene.set_profiling(True)
+            scene.clear(); scene.set_light_direction(v[9:12]); scene.set_camera(v[0:3], v[3:6], v[6:9]); scene.render()
+        scene.synchronize()
+        scene.set_profiling(False)
+    kt = scene.kernel_times()       # (the launch counts include the unprofiled frames: divide by the profiled ones)
+    return {k: (t / (len(views) * frames) * 1e3) for k, (t, n) in kt.items() if n and t > 0}
+
+
 def timed_batches(torch, dist, tstream, pstreams, call, steps, preroll=1):
     """`steps` x call() between CUDA events on tstream, the scenes' streams forked from / joined into it; a barrier and a
     device synchronize on both sides; returns ms (this rank)."""
@@ -847,6 +865,7 @@ def run_gpu(args, rank, world, local_rank):
             s.set_debug_flags(2)                             # lone frames in the batch CTA shape (128 threads)
             per[p]["128"] = lone_frame_us(s, sample)
             s.set_debug_flags(0)
+            per[p]["256_settled"] = settled_frame_us(s, sample)
         line["kernel_us"] = per
         cov8 = float(np.mean(cov[::8]))
         ab = {p: algorithmic_bytes(n_px, cov8, n_tri, p) for p in PIPES}
@@ -863,7 +882,7 @@ def run_gpu(args, rank, world, local_rank):
 
         def frame_fig(p, shape):
             us = sum(per[p][shape].get(k, 0.0) for k in ("K1_vertex_setup", "K3_raster_visibility"))
-            return {"cta_threads": int(shape), "algorithmic_bytes": ab[p]["frame"], "us": us,
+            return {"cta_threads": int(shape.split("_")[0]), "algorithmic_bytes": ab[p]["frame"], "us": us,
                     "achieved": ab[p]["frame"] / (us * 1e-6) / 1e9, "frac": ab[p]["frame"] / (us * 1e-6) / 1e9 / peak}
 
         k = kernel_fig(dom, "128")
@@ -893,8 +912,12 @@ def run_gpu(args, rank, world, local_rank):
                                % (tsrc, (steady or {}).get("launches"))) if steady else "per-launch ncu capture of this kernel (serialised)",
             "algorithmic_bytes_per_launch": k["algorithmic_bytes_per_launch"], "us_per_launch": k["us_per_launch"], "issue": k["issue"],
             "kernels": {p + "," + sh: kernel_fig(p, sh) for p in PIPES for sh in ("128", "256")},
-            "frame_serial": dict(frame_fig(dom, "256"), note="lone darboux frame K1 + K3/K5, 256-thread shape (what tr_scene_render launches)"),
-            "frame_serial_phong": frame_fig("phong", "256"),
+            "frame_serial": dict(frame_fig(dom, "256_settled"), cta_threads=256,
+                                 note="lone darboux frame K1 + K3/K5, 256-thread shape (what tr_scene_render launches), view settled as in the "
+                                      "reference's app loop (< 0.1 degree per frame): tiles launched in the order of their cost in the previous frame"),
+            "frame_serial_phong": dict(frame_fig("phong", "256_settled"), cta_threads=256),
+            "frame_serial_new_view": dict(frame_fig(dom, "256"), note="the same with every frame 45 degrees from the last: static centre-out launch order"),
+            "frame_serial_new_view_phong": frame_fig("phong", "256"),
             "batch": {"algorithmic_bytes_per_frame": batch_bytes, "us_per_frame": us_frame, "achieved": batch_bytes / (us_frame * 1e-6) / 1e9,
                       "frac": batch_bytes / (us_frame * 1e-6) / 1e9 / peak,
                       "note": "the timed region: both pipelines' frames overlapped, 128-thread shape",

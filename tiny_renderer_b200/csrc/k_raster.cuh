@@ -91,7 +91,7 @@ struct RasterArgs {
     // set-up kernel of the NEXT lone frame sorts the launch order by it, longest first (k_setup.cuh: sort_tiles).  Non-null
     // also means that tile_order was written by the set-up kernel in front of this launch, i.e. is read after the wait.
     uint32_t* tile_cost;
-    const uint32_t* tile_rank; // tile index -> its position in the static centre-out order (the index tile_cost is kept under)
+    const uint32_t* tile_perm; // launch position -> position in the static centre-out order (the index tile_cost is kept under); null: the same
 };
 
 // The tile is cut into kBlocksX x kBlocksY blocks of 8 x kBlockH pixels (one warp pass each); bit (by * kBlocksX + bx)
@@ -539,10 +539,19 @@ template <class PIPE, int THREADS>
 __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa, const Uniforms u, const __grid_constant__ CUtensorMap rgb_map,
                                          const __grid_constant__ CUtensorMap rgb_map_top) {
     constexpr bool LONE = THREADS == kRasterThreads;
-    __shared__ uint32_t s_t0;          // (shared, not a register: the tile code's register budget is exhausted)
+    // (shared, not registers: the tile code's register budget is exhausted.  The tile's index into tile_cost arrives by an
+    // asynchronous copy, so that no thread waits for it: a CTA of an empty tile lives for half a microsecond, and
+    // two dependent loads at its end would treble that for 2,900 of the 4,080 CTAs of a 4K frame)
+    __shared__ uint32_t s_t0, s_rank;
     if (LONE && a.tile_cost != nullptr) {
         asm volatile("griddepcontrol.wait;" ::: "memory");     // the launch order is the set-up kernel's output
-        if (threadIdx.x == 0) s_t0 = (uint32_t)clock();
+        if (threadIdx.x == 0) {
+            s_t0 = (uint32_t)clock();
+            if (a.tile_perm != nullptr)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(&s_rank)), "l"(a.tile_perm + blockIdx.x) : "memory");
+            else
+                s_rank = blockIdx.x;
+        }
     }
     TR_TIMELINE_MARK(blockIdx.x, 0, timeline_now());
     raster_tile<PIPE, THREADS>(a, sa, u, &rgb_map, &rgb_map_top, blockIdx.x);
@@ -553,8 +562,8 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     TR_TIMELINE_MARK(blockIdx.x, 4, (unsigned long long)sm);
 #endif
     if (LONE && a.tile_cost != nullptr && threadIdx.x == 0) {
-        const uint32_t xy = __ldg(&a.tile_order[blockIdx.x]);
-        a.tile_cost[__ldg(&a.tile_rank[(xy >> 16) * a.tiles_x + (xy & 0xffffu)])] = (uint32_t)clock() - s_t0;
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        a.tile_cost[s_rank] = (uint32_t)clock() - s_t0;
     }
 }
 

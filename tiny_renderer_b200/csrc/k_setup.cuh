@@ -19,6 +19,7 @@ struct TileSort {
     const uint32_t* cost;     // per centre-out position: SM cycles of that tile in the previous lone launch of this pass (k_raster.cuh)
     const uint32_t* base;     // n_tiles launch positions -> y << 16 | x, centre-out (ties keep this order)
     uint32_t* order;          // out: n_tiles entries, a permutation of base
+    uint32_t* perm;           // out: the centre-out position of every entry of order (where the tile kernel files its cost)
     uint32_t n_tiles;
 };
 constexpr int kSortBuckets = 16, kSortShift = 13;        // 8,192 cycles (4.2 us) per bucket: as good as an exact sort (probe)
@@ -79,7 +80,11 @@ __device__ __forceinline__ void sort_tiles(const TileSort& q) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             const uint32_t p = i0 + 32u * j + lane;
-            if (p < w1) q.order[atomicAdd(&s_run[s_bucket[p] * 4 + warp], 1u)] = xy[j];
+            if (p < w1) {
+                const uint32_t slot = atomicAdd(&s_run[s_bucket[p] * 4 + warp], 1u);
+                q.order[slot] = xy[j];
+                q.perm[slot] = p;
+            }
         }
     }
 }
@@ -225,10 +230,27 @@ __device__ __forceinline__ void vertex_setup(const float4* __restrict__ geom, co
 
 // SORT: the lone-frame form, whose last block writes the tile kernel's launch order (sort_tiles; 25 KB of shared memory
 // that the batch form, resident beside other frames' tile kernels, does not carry).
+#ifdef TR_TIMELINE
+// Diagnostic build only: per block of the last set-up launch, [0] entry and [1] exit (globaltimer, ns); block 255 = the sort block.
+__device__ unsigned long long g_timeline_setup[256 * 2];
+#endif
 template <bool LIGHT_PASS, bool SORT = false>
 __global__ void __launch_bounds__(128) k_vertex_setup(const float4* __restrict__ geom, const SetupOut out, const Uniforms u, int pipeline,
                                                      unsigned long long* diag) {
+#ifdef TR_TIMELINE
+    unsigned long long t_in;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_in));
+#endif
     vertex_setup<LIGHT_PASS, SORT>(geom, out, u, pipeline, diag);
+#ifdef TR_TIMELINE
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t_out;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_out));
+        const int slot = (SORT && out.sort.cost != nullptr && blockIdx.x == gridDim.x - 1) ? 255 : min((int)blockIdx.x, 254);
+        g_timeline_setup[2 * slot] = t_in; g_timeline_setup[2 * slot + 1] = t_out;
+    }
+#endif
 }
 
 // Several views in one launch (see k_raster_views): blockIdx.y selects the view's uniforms and frame slot.

@@ -75,9 +75,13 @@ struct tr_scene {
     // lone frames: per pass (0 light depth, 1 camera) the tiles' cost in the last lone launch and the launch order the
     // set-up kernel sorts from it (k_setup.cuh: sort_tiles); order_sorted[p]: the set-up kernel in front wrote order p
     uint32_t* tile_cost = nullptr;       // [pass][centre-out position]
-    uint32_t* tile_rank = nullptr;       // tile index -> centre-out position
+    uint32_t* tile_perm = nullptr;       // [pass][launch position of the sorted order] -> centre-out position
     uint32_t* tile_order_sorted = nullptr;
     bool order_sorted[2] = {false, false};
+    // the view (eye or light, target, up) whose lone frame left tile_cost[p] behind; the sorted order is only used for a
+    // view close to it (view_close)
+    struct CostView { f3 eye{0, 0, 0}, at{0, 0, 0}, up{0, 0, 0}; bool valid = false; } cost_view[2];
+    CostView last_view[2];             // the view of the previous lone frame: costs are only recorded once the view has settled
     bool overlapping = false;            // a batch is running frames / light passes concurrently on the slot streams
     uint32_t debug_flags = 0;            // tr_scene_set_debug_flags -> Uniforms::debug_flags
     uint32_t* ao = nullptr;            // n_px sums, zero padding to a multiple of 4, then the kPeerFlagWords barrier flags of K9
@@ -354,10 +358,8 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
 #endif
         CU(cudaMalloc(&s->tile_order, packed.size() * 4));
         CU(cudaMemcpy(s->tile_order, packed.data(), packed.size() * 4, cudaMemcpyHostToDevice));
-        std::vector<uint32_t> rank(n_tiles);
-        for (size_t i = 0; i < n_tiles; ++i) rank[order[i]] = (uint32_t)i;
-        CU(cudaMalloc(&s->tile_rank, n_tiles * 4));
-        CU(cudaMemcpy(s->tile_rank, rank.data(), n_tiles * 4, cudaMemcpyHostToDevice));
+        CU(cudaMalloc(&s->tile_perm, 2 * n_tiles * 4));
+        CU(cudaMemset(s->tile_perm, 0, 2 * n_tiles * 4));
         CU(cudaMalloc(&s->tile_cost, 2 * n_tiles * 4));
         CU(cudaMemset(s->tile_cost, 0, 2 * n_tiles * 4));
         CU(cudaMalloc(&s->tile_order_sorted, 2 * n_tiles * 4));
@@ -453,7 +455,7 @@ void destroy_impl(tr_scene* s) {
         cudaFree(sl.cam.rec); cudaFree(sl.cam.var); cudaFree(sl.cam.bbox); cudaFree(sl.lit.rec); cudaFree(sl.lit.bbox);
         cudaFree(sl.bins.count); cudaFree(sl.bins.list);
     }
-    cudaFree(s->geom); cudaFree(s->tile_order); cudaFree(s->tile_cost); cudaFree(s->tile_rank); cudaFree(s->tile_order_sorted); if (!s->ao_vmm) cudaFree(s->ao); cudaFree(s->ao_list.frag); cudaFree(s->ao_list.pix); cudaFree(s->ao_list.count); cudaFree(s->diag); cudaFree(s->host_stats); cudaFree(s->d_checksums); cudaFree(s->scratch);
+    cudaFree(s->geom); cudaFree(s->tile_order); cudaFree(s->tile_cost); cudaFree(s->tile_perm); cudaFree(s->tile_order_sorted); if (!s->ao_vmm) cudaFree(s->ao); cudaFree(s->ao_list.frag); cudaFree(s->ao_list.pix); cudaFree(s->ao_list.count); cudaFree(s->diag); cudaFree(s->host_stats); cudaFree(s->d_checksums); cudaFree(s->scratch);
     if (s->own_stream) cudaStreamDestroy(s->own_stream);
     delete s;
 }
@@ -464,6 +466,31 @@ void destroy_impl(tr_scene* s) {
 // batch shape.  TINYR_LONE_SORT=0: lone frames keep the static centre-out launch order (A/B in profiles/r2_probes.md).
 static const bool g_lone_sort = !(getenv("TINYR_LONE_SORT") && atoi(getenv("TINYR_LONE_SORT")) == 0);
 bool lone_shape(const tr_scene* s) { return !s->overlapping && (s->debug_flags & 2u) == 0u; }
+// lone frames of at least two waves of tiles (800x800: 325 tiles, one wave whatever the order) record tile costs
+bool lone_costs(const tr_scene* s) {
+    const uint32_t n_tiles = s->tiles_x * s->tiles_y;
+    return lone_shape(s) && g_lone_sort && n_tiles > 1024u && n_tiles <= (uint32_t)kSortMaxTiles;
+}
+tr_scene::CostView pass_view(const tr_scene* s, int pass) {
+    tr_scene::CostView v;
+    v.eye = pass == 0 ? f3{s->at.x + s->light.x, s->at.y + s->light.y, s->at.z + s->light.z} : s->from;
+    v.at = s->at; v.up = s->up; v.valid = true;
+    return v;
+}
+// The previous frame's costs predict this frame's when the view moved little: measured on the 4K turntable, 1 degree per
+// frame keeps most of the gain of a still view, 5.6 degrees per frame has none left (profiles/r2_probes.md); the
+// reference's app loop turns the camera by 3 rad/s x frame time (app.rs:12,178), i.e. well under 0.1 degree per frame.
+bool view_close(const tr_scene::CostView& a, const tr_scene::CostView& b) {
+    if (!a.valid || !b.valid) return false;
+    const double kCos = 0.99905;           // cos(2.5 degrees)
+    auto sub = [](f3 p, f3 q) { return f3{p.x - q.x, p.y - q.y, p.z - q.z}; };
+    auto dot = [](f3 p, f3 q) { return (double)p.x * q.x + (double)p.y * q.y + (double)p.z * q.z; };
+    const f3 da = sub(a.eye, a.at), db = sub(b.eye, b.at), dt = sub(a.at, b.at);
+    const double la = std::sqrt(dot(da, da)), lb = std::sqrt(dot(db, db)), ua = std::sqrt(dot(a.up, a.up)), ub = std::sqrt(dot(b.up, b.up));
+    if (!(la > 0.0 && lb > 0.0 && ua > 0.0 && ub > 0.0)) return false;
+    return dot(da, db) >= kCos * la * lb && dot(a.up, b.up) >= kCos * ua * ub && std::fabs(la / lb - 1.0) <= 0.03 &&
+           std::sqrt(dot(dt, dt)) <= 0.03 * lb;
+}
 
 int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     if (s->n_tri == 0) return TR_OK;
@@ -476,13 +503,13 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     const int pass = light_pass ? 0 : 1;
     const uint32_t n_tiles = s->tiles_x * s->tiles_y;
     s->order_sorted[pass] = false;
-    // (frames of fewer tiles than the device holds CTAs at once — 800x800: 325 — run as one wave, whatever the order)
-    if (lone_shape(s) && g_lone_sort && n_tiles > 1024u && n_tiles <= (uint32_t)kSortMaxTiles) {
+    if (lone_costs(s) && view_close(s->cost_view[pass], pass_view(s, pass))) {
         // a lone frame: one more block sorts the tile kernel's launch order by the tiles' cost in the previous lone frame
         SetupOut out = light_pass ? S(s).lit : S(s).cam;
         out.sort.cost = s->tile_cost + (size_t)pass * n_tiles;
         out.sort.base = s->tile_order;
         out.sort.order = s->tile_order_sorted + (size_t)pass * n_tiles;
+        out.sort.perm = s->tile_perm + (size_t)pass * n_tiles;
         out.sort.n_tiles = n_tiles;
         grid.x += 1;
         if (light_pass) k_vertex_setup<true, true><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->pipeline, s->diag);
@@ -608,10 +635,19 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     // CTA shape: 256 threads for a lone frame, 128 for overlapped batches (k_raster.cuh)
     const int shape = lone_shape(s) ? 0 : 1;      // (debug bit 1: time the batch shape on a lone frame)
     const int pass = depth_only ? 0 : 1;
-    if (shape == 0 && s->order_sorted[pass]) {
-        a.tile_order = s->tile_order_sorted + (size_t)pass * a.n_tiles;
-        a.tile_cost = s->tile_cost + (size_t)pass * a.n_tiles;
-        a.tile_rank = s->tile_rank;
+    if (lone_costs(s)) {
+        if (s->order_sorted[pass]) {
+            a.tile_order = s->tile_order_sorted + (size_t)pass * a.n_tiles;
+            a.tile_perm = s->tile_perm + (size_t)pass * a.n_tiles;
+        }
+        // (a view that moves fast — 5.6 degrees per frame on the bench's turntable — records nothing and pays nothing:
+        // the recording costs such a frame about 1 us; a view that has settled is sorted from its third frame on)
+        const tr_scene::CostView now = pass_view(s, pass);
+        if (s->order_sorted[pass] || view_close(s->last_view[pass], now)) {
+            a.tile_cost = s->tile_cost + (size_t)pass * a.n_tiles;
+            s->cost_view[pass] = now;
+        }
+        s->last_view[pass] = now;
     }
     s->order_sorted[pass] = false;
     if (mode == kModeDepthOnly) kRasterLightDepth[shape](s, grid, a, sa, u);
@@ -903,6 +939,12 @@ extern "C" int tr_debug_timeline(uint64_t* out, uint32_t n_ctas) {
     if (!out || n_ctas > (uint32_t)kTimelineCtas) return fail(TR_ERR_INVALID_ARGUMENT, "tr_debug_timeline: bad argument");
     CU(cudaDeviceSynchronize());
     CU(cudaMemcpyFromSymbol(out, g_timeline, (size_t)n_ctas * kTimelineWords * 8));
+    return TR_OK;
+}
+extern "C" int tr_debug_timeline_setup(uint64_t* out512) {
+    using namespace tr;
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpyFromSymbol(out512, g_timeline_setup, 512 * 8));
     return TR_OK;
 }
 #endif

@@ -46,6 +46,10 @@ for pipe in sys.argv[1:] or ["phong", "darboux"]:
     g.synchronize()
     tl = np.zeros((n_tiles, WORDS), np.uint64)
     assert L.tr_debug_timeline(tl.ctypes.data, n_tiles) == 0
+    ts = np.zeros(512, np.uint64)
+    if hasattr(L, "tr_debug_timeline_setup"):
+        L.tr_debug_timeline_setup.argtypes = [ctypes.c_void_p]
+        L.tr_debug_timeline_setup(ts.ctypes.data)
     g.close()
     if os.environ.get("TIMELINE_DUMP"):
         np.save(os.path.join(os.environ["TIMELINE_DUMP"], "timeline_%s.npy" % pipe), tl)
@@ -59,6 +63,12 @@ for pipe in sys.argv[1:] or ["phong", "darboux"]:
            "wait_released_us": round(float(waited.min()), 1),
            "ctas_resident_before_release": int((entry < waited.min()).sum()),
            "after_release_us": round(float(end.max() - waited.min()), 1)}
+    k1 = ts.astype(np.int64).reshape(256, 2)
+    used = k1[:255, 0] > 0
+    if used.any():      # the vertex set-up kernel in front, on the tile kernel's clock (us, 0 = first tile CTA's entry)
+        out["setup_kernel_us"] = {"blocks": int(used.sum()), "first_entry": round(float((k1[:255, 0][used].min() - t0) / 1e3), 1),
+                                  "last_vertex_block_exit": round(float((k1[:255, 1][used].max() - t0) / 1e3), 1),
+                                  "sort_block_entry_exit": [round(float((k1[255, 0] - t0) / 1e3), 1), round(float((k1[255, 1] - t0) / 1e3), 1)] if k1[255, 0] > 0 else None}
     d = dur[touched]
     out["touched_tile_us"] = {"sum": round(float(d.sum()), 0), "p10": round(pct(d, 10), 1), "p50": round(pct(d, 50), 1), "p90": round(pct(d, 90), 1),
                               "max": round(float(d.max()), 1)}
