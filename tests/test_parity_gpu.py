@@ -452,13 +452,16 @@ def test_lone_4k_frames_in_a_row_launch_order_follows_the_previous_frame(tinyr, 
     g = Scene(w, h, model, pipeline)
     o = oracle.OracleScene(w, h, model, pipeline)
     two = pipeline in TWO_PASS
-    for step, (cam, light) in enumerate([(0.4, 0.7), (0.4, 0.7), (3.3, 2.1), (1.9, 0.2)]):
+    # four frames of one view (from the third on the launch order follows the previous frame's costs), the same view
+    # again WITHOUT a clear, a view one degree on, then very different ones
+    seq = [(0.4, 0.7, True)] * 4 + [(0.4, 0.7, False), (0.4 + math.pi / 180, 0.7, True), (3.3, 2.1, True), (1.9, 0.2, True), (1.9, 0.2, True), (1.9, 0.2, True)]
+    for step, (cam, light, clear) in enumerate(seq):
         lf, la, up, l = assets.view_vectors(cam, light)
-        if step == 2:       # a very different frame in between (camera turned away: the model projects mirrored, no clipping)
+        if step == 6:       # a very different frame in between (camera turned away: the model projects mirrored, no clipping)
             away = (lf[0] * 3.0, lf[1] * 3.0, lf[2] * 3.0)
             parity.drive(g, lf, away, up, l)
-        parity.drive(g, lf, la, up, l)
-        parity.drive(o, lf, la, up, l)
+        parity.drive(g, lf, la, up, l, clear=clear)
+        parity.drive(o, lf, la, up, l, clear=clear)
         st = parity.compare(g, o, two_pass=two)
         assert st["rgb_exact_frac"] == 1.0 and st["depth_bits_differ"] == 0, (step, st)
     g.close()
