@@ -80,7 +80,9 @@ struct tr_scene {
     bool order_sorted[2] = {false, false};
     // the view (eye or light, target, up) whose lone frame left tile_cost[p] behind; the sorted order is only used for a
     // view close to it (view_close)
-    struct CostView { f3 eye{0, 0, 0}, at{0, 0, 0}, up{0, 0, 0}; bool valid = false; } cost_view[2];
+    struct CostView { f3 eye{0, 0, 0}, at{0, 0, 0}, up{0, 0, 0}; int pipeline = -1; bool valid = false; } cost_view[2];
+    CostView order_view[2];            // the view the sorted order of pass p was last built for, and how often in a row:
+    uint32_t order_builds[2] = {0, 0}; // a view that stands still is sorted twice (the second time from a sorted frame's costs), then re-uses the order
     CostView last_view[2];             // the view of the previous lone frame: costs are only recorded once the view has settled
     bool overlapping = false;            // a batch is running frames / light passes concurrently on the slot streams
     uint32_t debug_flags = 0;            // tr_scene_set_debug_flags -> Uniforms::debug_flags
@@ -474,8 +476,12 @@ bool lone_costs(const tr_scene* s) {
 tr_scene::CostView pass_view(const tr_scene* s, int pass) {
     tr_scene::CostView v;
     v.eye = pass == 0 ? f3{s->at.x + s->light.x, s->at.y + s->light.y, s->at.z + s->light.z} : s->from;
-    v.at = s->at; v.up = s->up; v.valid = true;
+    v.at = s->at; v.up = s->up; v.pipeline = s->pipeline; v.valid = true;
     return v;
+}
+bool view_same(const tr_scene::CostView& a, const tr_scene::CostView& b) {
+    auto eq = [](f3 p, f3 q) { return p.x == q.x && p.y == q.y && p.z == q.z; };
+    return a.valid && b.valid && a.pipeline == b.pipeline && eq(a.eye, b.eye) && eq(a.at, b.at) && eq(a.up, b.up);
 }
 // The previous frame's costs predict this frame's when the view moved little: measured on the 4K turntable, 1 degree per
 // frame keeps most of the gain of a still view, 5.6 degrees per frame has none left (profiles/r2_probes.md); the
@@ -503,8 +509,15 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     const int pass = light_pass ? 0 : 1;
     const uint32_t n_tiles = s->tiles_x * s->tiles_y;
     s->order_sorted[pass] = false;
-    if (lone_costs(s) && view_close(s->cost_view[pass], pass_view(s, pass))) {
+    const tr_scene::CostView now = pass_view(s, pass);
+    if (lone_costs(s) && view_close(s->cost_view[pass], now) && view_same(s->order_view[pass], now) && s->order_builds[pass] >= 2) {
+        // a view that stands still (the app loop with no key down): the order built for it stands too.  The sort block
+        // ends 4 us after the vertex blocks (k_setup.cuh), which a frame that needs no new order does not have to wait for.
+        s->order_sorted[pass] = true;
+    } else if (lone_costs(s) && view_close(s->cost_view[pass], now)) {
         // a lone frame: one more block sorts the tile kernel's launch order by the tiles' cost in the previous lone frame
+        s->order_builds[pass] = view_same(s->order_view[pass], now) ? s->order_builds[pass] + 1 : 1;
+        s->order_view[pass] = now;
         SetupOut out = light_pass ? S(s).lit : S(s).cam;
         out.sort.cost = s->tile_cost + (size_t)pass * n_tiles;
         out.sort.base = s->tile_order;
@@ -516,6 +529,8 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
         else k_vertex_setup<false, true><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->pipeline, s->diag);
         s->order_sorted[pass] = true;
         return launch_ok("k_vertex_setup");
+    } else {
+        s->order_builds[pass] = 0;          // (a frame with the static order in between: whatever order exists is stale)
     }
     if (light_pass) k_vertex_setup<true><<<grid, 128, 0, s->stream>>>(s->geom, S(s).lit, u, s->pipeline, s->diag);
     else k_vertex_setup<false><<<grid, 128, 0, s->stream>>>(s->geom, S(s).cam, u, s->pipeline, s->diag);
@@ -945,6 +960,12 @@ extern "C" int tr_debug_timeline_setup(uint64_t* out512) {
     using namespace tr;
     CU(cudaDeviceSynchronize());
     CU(cudaMemcpyFromSymbol(out512, g_timeline_setup, 512 * 8));
+    return TR_OK;
+}
+extern "C" int tr_debug_timeline_phase(uint64_t* out1024) {
+    using namespace tr;
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpyFromSymbol(out1024, g_timeline_phase, 1024 * 8));
     return TR_OK;
 }
 #endif

@@ -50,6 +50,10 @@ for pipe in sys.argv[1:] or ["phong", "darboux"]:
     if hasattr(L, "tr_debug_timeline_setup"):
         L.tr_debug_timeline_setup.argtypes = [ctypes.c_void_p]
         L.tr_debug_timeline_setup(ts.ctypes.data)
+    ph = np.zeros(1024, np.uint64)
+    if hasattr(L, "tr_debug_timeline_phase"):
+        L.tr_debug_timeline_phase.argtypes = [ctypes.c_void_p]
+        L.tr_debug_timeline_phase(ph.ctypes.data)
     g.close()
     if os.environ.get("TIMELINE_DUMP"):
         np.save(os.path.join(os.environ["TIMELINE_DUMP"], "timeline_%s.npy" % pipe), tl)
@@ -69,6 +73,23 @@ for pipe in sys.argv[1:] or ["phong", "darboux"]:
         out["setup_kernel_us"] = {"blocks": int(used.sum()), "first_entry": round(float((k1[:255, 0][used].min() - t0) / 1e3), 1),
                                   "last_vertex_block_exit": round(float((k1[:255, 1][used].max() - t0) / 1e3), 1),
                                   "sort_block_entry_exit": [round(float((k1[255, 0] - t0) / 1e3), 1), round(float((k1[255, 1] - t0) / 1e3), 1)] if k1[255, 0] > 0 else None}
+    if used.any() and ph.any():     # thread 0 of every vertex block: us after the block's entry
+        p4 = ph.astype(np.int64).reshape(256, 4)[:255][used]
+        rel = (p4 - k1[:255, 0][used][:, None]) / 1e3
+        ent = (k1[:255, 0][used] - k1[:255, 0][used].min()) / 1e3
+        life = (k1[:255, 1][used] - k1[:255, 0][used]) / 1e3
+        out["setup_blocks_entry_us_min_med_max"] = [round(float(ent.min()), 2), round(float(np.median(ent)), 2), round(float(ent.max()), 2)]
+        out["setup_blocks_life_us_min_med_max"] = [round(float(life.min()), 2), round(float(np.median(life)), 2), round(float(life.max()), 2)]
+        slow = np.argsort(-life)[:4]
+        out["setup_slowest_blocks"] = [{"block": int(b), "entry": round(float(ent[b]), 2), "life": round(float(life[b]), 2),
+                                        "phases": [round(float(x), 2) for x in rel[b]]} for b in slow]
+        if k1[255, 0] > 0:
+            sp = (ph.astype(np.int64).reshape(256, 4)[255] - k1[255, 0]) / 1e3
+            out["sort_block_phases_us"] = {"zeroed_and_loads_issued": round(float(sp[0]), 2), "counted": round(float(sp[1]), 2), "prefix": round(float(sp[2]), 2),
+                                           "scattered": round(float(sp[3]), 2), "exit": round(float((k1[255, 1] - k1[255, 0]) / 1e3), 2)}
+        out["setup_block_phases_us_median"] = {"geometry_loaded": round(float(np.median(rel[:, 0])), 2), "transformed": round(float(np.median(rel[:, 1])), 2),
+                                               "binned": round(float(np.median(rel[:, 2])), 2), "records_issued": round(float(np.median(rel[:, 3])), 2),
+                                               "exit": round(float(np.median((k1[:255, 1][used] - k1[:255, 0][used]) / 1e3)), 2)}
     d = dur[touched]
     out["touched_tile_us"] = {"sum": round(float(d.sum()), 0), "p10": round(pct(d, 10), 1), "p50": round(pct(d, 50), 1), "p90": round(pct(d, 90), 1),
                               "max": round(float(d.max()), 1)}
