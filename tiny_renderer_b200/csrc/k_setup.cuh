@@ -48,7 +48,9 @@ __device__ unsigned long long g_timeline_phase[256 * 4];
 // Measured (per-block timeline, profiles/r2_probes.md): 8.3 us against 4.0 us for the slowest vertex block — 3.2 us counting
 // and 3.3 us scattering, because three quarters of the tiles fall into the last bucket, i.e. onto four addresses.  A form
 // without atomics (a private counter column per thread over contiguous positions, shuffle scans) was slower still, 13.7 us:
-// its loads no longer coalesce.  The host therefore sorts once per view and re-uses the order while the view stands still.
+// its loads no longer coalesce; serving the lanes of the last bucket (or, with match.any, of every bucket) with one atomic
+// per step was slower too, 10.6 and 10.9 us.  The host therefore sorts twice per view and re-uses the order while the
+// view stands still.
 __device__ __forceinline__ uint32_t sort_bucket(uint32_t cycles) {        // bucket 0 = longest
     return (uint32_t)(kSortBuckets - 1) - min((uint32_t)(kSortBuckets - 1), cycles >> kSortShift);
 }
