@@ -465,3 +465,28 @@ def test_lone_4k_frames_in_a_row_launch_order_follows_the_previous_frame(tinyr, 
         st = parity.compare(g, o, two_pass=two)
         assert st["rgb_exact_frac"] == 1.0 and st["depth_bits_differ"] == 0, (step, st)
     g.close()
+
+
+@pytest.mark.parametrize("size", [(2100, 1100), (7680, 4320)])
+def test_sorted_launch_order_at_other_tile_counts(tinyr, oracle, size):
+    """The sort block of the set-up kernel handles its positions in rounds of 4,096 (k_setup.cuh): 1,155 tiles (a ragged
+    last round, a partial top tile row) and 16,200 tiles (four rounds, the 8K frame of config 5) — still views, so frames
+    three and four run with the sorted and then the re-used order."""
+    from tiny_renderer_b200.scene import Scene
+    model = get_model("diablo")
+    w, h = size
+    g = Scene(w, h, model, "phong")
+    o = oracle.OracleScene(w, h, model, "phong")
+    lf, la, up, l = assets.view_vectors(0.9, 0.7)
+    parity.drive(o, lf, la, up, l)
+    for step in range(5):
+        parity.drive(g, lf, la, up, l)
+        if step >= 2:
+            st = parity.compare(g, o)
+            assert st["rgb_exact_frac"] == 1.0 and st["depth_bits_differ"] == 0, (step, st)
+    lf, la, up, l = assets.view_vectors(0.9 + math.pi / 360, 0.7)        # half a degree on: sorted by the old view's costs
+    parity.drive(g, lf, la, up, l)
+    parity.drive(o, lf, la, up, l)
+    st = parity.compare(g, o)
+    assert st["rgb_exact_frac"] == 1.0 and st["depth_bits_differ"] == 0, st
+    g.close()
