@@ -83,6 +83,7 @@ struct tr_scene {
     struct CostView { f3 eye{0, 0, 0}, at{0, 0, 0}, up{0, 0, 0}; int pipeline = -1; bool valid = false; } cost_view[2];
     CostView order_view[2];            // the view the sorted order of pass p was last built for, and how often in a row:
     uint32_t order_builds[2] = {0, 0}; // a view that stands still is sorted twice (the second time from a sorted frame's costs), then re-uses the order
+    uint32_t order_uses[2] = {0, 0};   // frames since the order was last built (it is rebuilt every 256 frames: costs recorded under a disturbance do not stick)
     CostView last_view[2];             // the view of the previous lone frame: costs are only recorded once the view has settled
     bool overlapping = false;            // a batch is running frames / light passes concurrently on the slot streams
     uint32_t debug_flags = 0;            // tr_scene_set_debug_flags -> Uniforms::debug_flags
@@ -510,7 +511,8 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     const uint32_t n_tiles = s->tiles_x * s->tiles_y;
     s->order_sorted[pass] = false;
     const tr_scene::CostView now = pass_view(s, pass);
-    if (lone_costs(s) && view_close(s->cost_view[pass], now) && view_same(s->order_view[pass], now) && s->order_builds[pass] >= 2) {
+    if (lone_costs(s) && view_close(s->cost_view[pass], now) && view_same(s->order_view[pass], now) && s->order_builds[pass] >= 2 &&
+        ++s->order_uses[pass] < 256u) {
         // a view that stands still (the app loop with no key down): the order built for it stands too.  The sort block
         // ends 4 us after the vertex blocks (k_setup.cuh), which a frame that needs no new order does not have to wait for.
         s->order_sorted[pass] = true;
@@ -518,6 +520,7 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
         // a lone frame: one more block sorts the tile kernel's launch order by the tiles' cost in the previous lone frame
         s->order_builds[pass] = view_same(s->order_view[pass], now) ? s->order_builds[pass] + 1 : 1;
         s->order_view[pass] = now;
+        s->order_uses[pass] = 0;
         SetupOut out = light_pass ? S(s).lit : S(s).cam;
         out.sort.cost = s->tile_cost + (size_t)pass * n_tiles;
         out.sort.base = s->tile_order;
