@@ -468,6 +468,7 @@ void destroy_impl(tr_scene* s) {
 // A lone frame (not part of an overlapped batch) runs the 256-thread tile kernel (k_raster.cuh); debug bit 1 forces the
 // batch shape.  TINYR_LONE_SORT=0: lone frames keep the static centre-out launch order (A/B in profiles/r2_probes.md).
 static const bool g_lone_sort = !(getenv("TINYR_LONE_SORT") && atoi(getenv("TINYR_LONE_SORT")) == 0);
+static const uint32_t g_order_builds = getenv("TINYR_ORDER_BUILDS") ? (uint32_t)atoi(getenv("TINYR_ORDER_BUILDS")) : 2u;
 bool lone_shape(const tr_scene* s) { return !s->overlapping && (s->debug_flags & 2u) == 0u; }
 // lone frames of at least two waves of tiles (800x800: 325 tiles, one wave whatever the order) record tile costs
 bool lone_costs(const tr_scene* s) {
@@ -511,7 +512,7 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     const uint32_t n_tiles = s->tiles_x * s->tiles_y;
     s->order_sorted[pass] = false;
     const tr_scene::CostView now = pass_view(s, pass);
-    if (lone_costs(s) && view_close(s->cost_view[pass], now) && view_same(s->order_view[pass], now) && s->order_builds[pass] >= 2 &&
+    if (lone_costs(s) && view_close(s->cost_view[pass], now) && view_same(s->order_view[pass], now) && s->order_builds[pass] >= g_order_builds &&
         ++s->order_uses[pass] < 256u) {
         // a view that stands still (the app loop with no key down): the order built for it stands too.  The sort block
         // ends 4 us after the vertex blocks (k_setup.cuh), which a frame that needs no new order does not have to wait for.
