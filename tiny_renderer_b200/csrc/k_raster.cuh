@@ -90,6 +90,9 @@ struct RasterArgs {
     // Lone-frame launches: per tile (under its position in the static centre-out order), the SM cycles this launch spent on it.  The vertex
     // set-up kernel of the NEXT lone frame sorts the launch order by it, longest first (k_setup.cuh: sort_tiles).  Non-null
     // also means that tile_order was written by the set-up kernel in front of this launch, i.e. is read after the wait.
+    // Lone frames: the diagnostics block of the set-up kernel run whose output this launch reads (possibly a run of an
+    // earlier frame of the same view, k_setup.cuh SetupOut::diag_zero); folded into diag once per launch.  Null: none.
+    const unsigned long long* setup_diag;
     uint32_t* tile_cost;
     const uint32_t* tile_perm; // launch position -> position in the static centre-out order (the index tile_cost is kept under); null: the same
 };
@@ -561,6 +564,10 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     TR_TIMELINE_MARK(blockIdx.x, 3, timeline_now());
     TR_TIMELINE_MARK(blockIdx.x, 4, (unsigned long long)sm);
 #endif
+    if (LONE && a.setup_diag != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {       // (behind raster_tile's wait for the set-up kernel)
+        const unsigned long long w_zero = a.setup_diag[D_W_ZERO];       // the only counter the set-up kernel feeds
+        if (w_zero) atomicAdd(&a.diag[D_W_ZERO], w_zero);
+    }
     if (LONE && a.tile_cost != nullptr && threadIdx.x == 0) {
         asm volatile("cp.async.wait_all;" ::: "memory");
         a.tile_cost[s_rank] = (uint32_t)clock() - s_t0;

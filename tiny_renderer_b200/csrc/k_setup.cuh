@@ -118,6 +118,10 @@ struct SetupOut {
     int4* bbox;       // n_triangles: xmin ymin xmax ymax clamped to the screen; xmin > xmax when not drawn
     Bins bins;        // K2: per-cell polygon lists for the raster kernel that follows
     TileSort sort;    // cost != null: the grid has one extra block that writes the tile kernel's launch order
+    // Lone camera passes whose output the host may re-use for the next frames of the same view (tinyr.cu: run_setup) count
+    // their diagnostics into a block of their own, which the tile kernel of every frame that uses this output folds
+    // into the scene's: `diag` then points at that block and diag_zero at the block of the NEXT run, cleared here.
+    unsigned long long* diag_zero;
 };
 
 // LIGHT_PASS: shadow/occlusion pass 1 — no culling, transform by u.shadow, no varyings.  Otherwise `pipeline` selects the
@@ -132,6 +136,7 @@ __device__ __forceinline__ void vertex_setup(const float4* __restrict__ geom, co
     // The tile kernel behind this one is launched with programmatic stream serialization (tinyr.cu: launch_raster): let
     // it start now; it waits for this grid's completion before it touches anything written here.
     asm volatile("griddepcontrol.launch_dependents;");
+    if (out.diag_zero != nullptr && blockIdx.x == 0 && threadIdx.x < D_COUNT) out.diag_zero[threadIdx.x] = 0ull;
     if (SORT && out.sort.cost != nullptr && blockIdx.x == gridDim.x - 1) {
         // the extra block: its share of the counter zeroing below, then the launch order
         uint32_t* other = out.bins.count + (out.bins.parity ^ 1u) * out.bins.n_cells;

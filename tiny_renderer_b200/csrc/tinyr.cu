@@ -63,6 +63,12 @@ struct tr_scene {
         CUtensorMap rgb_map_top{};         // same tensor, box as high as the partial tile row at the top of the frame
         bool rgb_tma = false;
         SetupOut cam{}, lit{};
+        // Re-use of a lone camera pass's set-up output (run_setup): what it was computed for, the diagnostics blocks of
+        // its runs (k_setup.cuh SetupOut::diag_zero) and how many runs there were
+        struct SetupKey { f3 from{0, 0, 0}, at{0, 0, 0}, up{0, 0, 0}, light{0, 0, 0}; int pipeline = -1; bool valid = false; } setup_key;
+        unsigned long long* setup_diag = nullptr;      // 2 x D_COUNT
+        uint32_t setup_runs = 0;
+        bool setup_reused = false;                     // the frame being queued re-uses the output (no set-up launch)
         Bins bins{};
         cudaStream_t stream = nullptr;
         cudaEvent_t done = nullptr;
@@ -394,6 +400,8 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
         CU(cudaMemset(sl.rgb_zero, 0, n_tiles * 4));
         CU(cudaMalloc(&sl.shadow_clear, n_tiles * 4));
         CU(cudaMemset(sl.shadow_clear, 0, n_tiles * 4));
+        CU(cudaMalloc(&sl.setup_diag, 2 * D_COUNT * 8));
+        CU(cudaMemset(sl.setup_diag, 0, 2 * D_COUNT * 8));
         if ((rc = make_rgb_map(s, &sl))) return rc;
         CU(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
@@ -454,7 +462,7 @@ void destroy_impl(tr_scene* s) {
     for (auto& sl : s->slots) {
         if (sl.stream) { cudaStreamSynchronize(sl.stream); cudaStreamDestroy(sl.stream); }
         if (sl.done) cudaEventDestroy(sl.done);
-        cudaFree(sl.keys); cudaFree(sl.tile_state); cudaFree(sl.rgb); cudaFree(sl.shadow); cudaFree(sl.rgb_zero); cudaFree(sl.shadow_clear);
+        cudaFree(sl.keys); cudaFree(sl.tile_state); cudaFree(sl.rgb); cudaFree(sl.shadow); cudaFree(sl.rgb_zero); cudaFree(sl.shadow_clear); cudaFree(sl.setup_diag);
         cudaFree(sl.cam.rec); cudaFree(sl.cam.var); cudaFree(sl.cam.bbox); cudaFree(sl.lit.rec); cudaFree(sl.lit.bbox);
         cudaFree(sl.bins.count); cudaFree(sl.bins.list);
     }
@@ -470,6 +478,12 @@ void destroy_impl(tr_scene* s) {
 static const bool g_lone_sort = !(getenv("TINYR_LONE_SORT") && atoi(getenv("TINYR_LONE_SORT")) == 0);
 static const uint32_t g_order_builds = getenv("TINYR_ORDER_BUILDS") ? (uint32_t)atoi(getenv("TINYR_ORDER_BUILDS")) : 2u;
 bool lone_shape(const tr_scene* s) { return !s->overlapping && (s->debug_flags & 2u) == 0u; }
+// TINYR_SETUP_CACHE=0: every lone frame runs the set-up kernel (A/B in profiles/r2_probes.md).
+static const bool g_setup_cache = !(getenv("TINYR_SETUP_CACHE") && atoi(getenv("TINYR_SETUP_CACHE")) == 0);
+bool setup_key_same(const tr_scene::Slot::SetupKey& a, const tr_scene::Slot::SetupKey& b) {
+    auto eq = [](f3 p, f3 q) { return p.x == q.x && p.y == q.y && p.z == q.z; };
+    return a.valid && b.valid && a.pipeline == b.pipeline && eq(a.from, b.from) && eq(a.at, b.at) && eq(a.up, b.up) && eq(a.light, b.light);
+}
 // lone frames of at least two waves of tiles (800x800: 325 tiles, one wave whatever the order) record tile costs
 bool lone_costs(const tr_scene* s) {
     const uint32_t n_tiles = s->tiles_x * s->tiles_y;
@@ -502,42 +516,66 @@ bool view_close(const tr_scene::CostView& a, const tr_scene::CostView& b) {
 
 int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     if (s->n_tri == 0) return TR_OK;
+    const int pass = light_pass ? 0 : 1;
+    const uint32_t n_tiles = s->tiles_x * s->tiles_y;
+    s->order_sorted[pass] = false;
+    S(s).setup_reused = false;
+    const tr_scene::CostView now = pass_view(s, pass);
+    // what this lone frame does about the tile kernel's launch order: re-use the one built for this very view, build one, or neither
+    const bool costs = lone_costs(s) && view_close(s->cost_view[pass], now);
+    const bool reuse_order = costs && view_same(s->order_view[pass], now) && s->order_builds[pass] >= g_order_builds && ++s->order_uses[pass] < 256u;
+    const bool build_order = costs && !reuse_order;
+    // The set-up output — records, varyings, bounding boxes, bins — is a pure function of model, pipeline, camera and light.
+    // A lone frame of a single-pass pipeline whose inputs equal, bit for bit, those of the set-up launch that last wrote
+    // this slot re-uses that output: no launch (the app loop with no key down re-renders one view; SURVEY.md 8(d) config 2
+    // times 100 frames of one view).  Two-pass pipelines share the bin lists between their passes and always run both.
+    tr_scene::Slot::SetupKey key;
+    key.from = s->from; key.at = s->at; key.up = s->up; key.light = s->light; key.pipeline = s->pipeline; key.valid = true;
+    const bool cacheable = g_setup_cache && lone_shape(s) && !light_pass && !kPipelines[s->pipeline].light_pass;
+    if (cacheable && !build_order && setup_key_same(S(s).setup_key, key)) {
+        S(s).setup_reused = true;
+        s->order_sorted[pass] = reuse_order;
+        return TR_OK;
+    }
     Scoped sp(s, KS_SETUP);
     dim3 grid((s->n_tri + 127) / 128);
     S(s).bins.parity ^= 1u;                 // this pass fills the other counter set; the kernel zeroes the one just used
     S(s).cam.bins = S(s).bins;
     S(s).lit.bins = S(s).bins;
     // (the vertex roles of all pipelines live in one kernel: k_setup.cuh)
-    const int pass = light_pass ? 0 : 1;
-    const uint32_t n_tiles = s->tiles_x * s->tiles_y;
-    s->order_sorted[pass] = false;
-    const tr_scene::CostView now = pass_view(s, pass);
-    if (lone_costs(s) && view_close(s->cost_view[pass], now) && view_same(s->order_view[pass], now) && s->order_builds[pass] >= g_order_builds &&
-        ++s->order_uses[pass] < 256u) {
+    SetupOut out = light_pass ? S(s).lit : S(s).cam;
+    unsigned long long* diag = s->diag;
+    S(s).setup_key.valid = false;
+    if (cacheable) {
+        S(s).setup_runs++;
+        diag = S(s).setup_diag + (size_t)(S(s).setup_runs & 1u) * D_COUNT;
+        out.diag_zero = S(s).setup_diag + (size_t)((S(s).setup_runs + 1u) & 1u) * D_COUNT;
+        S(s).setup_key = key;
+    }
+    if (reuse_order) {
         // a view that stands still (the app loop with no key down): the order built for it stands too.  The sort block
         // ends 4 us after the vertex blocks (k_setup.cuh), which a frame that needs no new order does not have to wait for.
         s->order_sorted[pass] = true;
-    } else if (lone_costs(s) && view_close(s->cost_view[pass], now)) {
-        // a lone frame: one more block sorts the tile kernel's launch order by the tiles' cost in the previous lone frame
+    } else if (build_order) {
+        // one more block sorts the tile kernel's launch order by the tiles' cost in the previous lone frame
         s->order_builds[pass] = view_same(s->order_view[pass], now) ? s->order_builds[pass] + 1 : 1;
         s->order_view[pass] = now;
         s->order_uses[pass] = 0;
-        SetupOut out = light_pass ? S(s).lit : S(s).cam;
         out.sort.cost = s->tile_cost + (size_t)pass * n_tiles;
         out.sort.base = s->tile_order;
         out.sort.order = s->tile_order_sorted + (size_t)pass * n_tiles;
         out.sort.perm = s->tile_perm + (size_t)pass * n_tiles;
         out.sort.n_tiles = n_tiles;
         grid.x += 1;
-        if (light_pass) k_vertex_setup<true, true><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->pipeline, s->diag);
-        else k_vertex_setup<false, true><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->pipeline, s->diag);
+        if (light_pass) k_vertex_setup<true, true><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->pipeline, diag);
+        else k_vertex_setup<false, true><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->pipeline, diag);
         s->order_sorted[pass] = true;
         return launch_ok("k_vertex_setup");
     } else {
         s->order_builds[pass] = 0;          // (a frame with the static order in between: whatever order exists is stale)
     }
-    if (light_pass) k_vertex_setup<true><<<grid, 128, 0, s->stream>>>(s->geom, S(s).lit, u, s->pipeline, s->diag);
-    else k_vertex_setup<false><<<grid, 128, 0, s->stream>>>(s->geom, S(s).cam, u, s->pipeline, s->diag);
+    if (light_pass) k_vertex_setup<true><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->pipeline, diag);
+    else k_vertex_setup<false><<<grid, 128, 0, s->stream>>>(s->geom, out, u, s->pipeline, diag);
     return launch_ok("k_vertex_setup");
 }
 
@@ -619,6 +657,7 @@ int run_views_multi(tr_scene* s, const uint32_t* slots, const Uniforms* lit, con
             S(s).bins.parity ^= 1u;
             S(s).cam.bins = S(s).bins;
             S(s).lit.bins = S(s).bins;
+            S(s).setup_key.valid = false;       // (the slot's set-up output is overwritten)
             sb.v[j].out = light ? S(s).lit : S(s).cam;
             sb.v[j].u = u;
             vb.v[j].a = raster_args(s, light, 0, true, true);
@@ -654,6 +693,8 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     // CTA shape: 256 threads for a lone frame, 128 for overlapped batches (k_raster.cuh)
     const int shape = lone_shape(s) ? 0 : 1;      // (debug bit 1: time the batch shape on a lone frame)
     const int pass = depth_only ? 0 : 1;
+    if (S(s).setup_key.valid && !depth_only)      // (valid: the slot's set-up output comes from a lone camera pass that counted into its own block)
+        a.setup_diag = S(s).setup_diag + (size_t)(S(s).setup_runs & 1u) * D_COUNT;
     if (lone_costs(s)) {
         if (s->order_sorted[pass]) {
             a.tile_order = s->tile_order_sorted + (size_t)pass * a.n_tiles;
