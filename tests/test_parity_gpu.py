@@ -490,3 +490,47 @@ def test_sorted_launch_order_at_other_tile_counts(tinyr, oracle, size):
     st = parity.compare(g, o)
     assert st["rgb_exact_frac"] == 1.0 and st["depth_bits_differ"] == 0, st
     g.close()
+
+
+def test_setup_output_is_reused_only_for_identical_inputs(tinyr, oracle):
+    """A lone frame of a single-pass pipeline re-uses the set-up kernel's output of the previous frame when camera, light
+    and pipeline are bit-identical (tinyr.cu run_setup).  Everything that changes the set-up output must bring the kernel
+    back: the light alone (vertex intensities), the pipeline (varyings), a view batch in between (it overwrites the
+    slot's records), another view and back."""
+    from tiny_renderer_b200.scene import Scene
+    model = get_model("diablo")
+    w, h = 2560, 1440
+    g = Scene(w, h, model, "phong", ring=2)
+    oracles = {p: oracle.OracleScene(w, h, model, p) for p in ("phong", "darboux")}
+    now = ["phong"]
+
+    def frame(cam, light, tag, clear=True):
+        lf, la, up, l = assets.view_vectors(cam, light)
+        o = oracles[now[0]]
+        parity.drive(g, lf, la, up, l, clear=clear)
+        parity.drive(o, lf, la, up, l, clear=clear)
+        st = parity.compare(g, o)
+        assert st["rgb_exact_frac"] == 1.0 and st["depth_bits_differ"] == 0, (tag, st)
+
+    for i in range(6):
+        frame(0.8, 0.7, ("still", i))
+    frame(0.8, 1.9, "light moved")
+    frame(0.8, 1.9, "light moved, again")
+    frame(0.8, 0.7, "light back")
+    g.set_pipeline("darboux"); now[0] = "darboux"
+    frame(0.8, 0.7, "pipeline changed")
+    frame(0.8, 0.7, "pipeline changed, again")
+    g.set_pipeline("phong"); now[0] = "phong"
+    frame(0.8, 0.7, "pipeline back")
+    frame(0.8, 0.7, "pipeline back, again")
+    # a view batch on the same scene overwrites the slots' set-up output
+    v = np.zeros((3, 12), np.float32)
+    for k in range(3):
+        lf, la, up, l = assets.view_vectors(2.0 + k, 0.3)
+        v[k, 0:3], v[k, 3:6], v[k, 6:9], v[k, 9:12] = lf, la, up, l
+    g.render_views(v)
+    frame(0.8, 0.7, "after a view batch")
+    frame(2.5, 0.7, "another view")
+    frame(0.8, 0.7, "and back")
+    frame(0.8, 0.7, "and back, no clear", clear=False)
+    g.close()
