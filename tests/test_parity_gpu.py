@@ -534,3 +534,41 @@ def test_setup_output_is_reused_only_for_identical_inputs(tinyr, oracle):
     frame(0.8, 0.7, "and back")
     frame(0.8, 0.7, "and back, no clear", clear=False)
     g.close()
+
+
+@pytest.mark.parametrize("pipeline", ["shadow", "occlusion"])
+def test_light_pass_is_reused_only_while_the_shadow_buffer_stands(tinyr, oracle, pipeline):
+    """Lone frames of the two-pass pipelines re-use the shadow buffer of the previous frame while light, target and up are
+    bit-identical and nothing else wrote to it (tinyr.cu render_impl): a camera that moves under a fixed light, frames
+    without a clear, a getter that materialises a pending clear in between, a light that moves and comes back."""
+    from tiny_renderer_b200.scene import Scene
+    model = get_model("diablo")
+    w, h = 2560, 1440
+    g = Scene(w, h, model, pipeline)
+    o = oracle.OracleScene(w, h, model, pipeline)
+
+    def frame(cam, light, tag, clear=True):
+        lf, la, up, l = assets.view_vectors(cam, light)
+        parity.drive(g, lf, la, up, l, clear=clear)
+        parity.drive(o, lf, la, up, l, clear=clear)
+        st = parity.compare(g, o, two_pass=True)
+        assert st["rgb_exact_frac"] == 1.0 and st["depth_bits_differ"] == 0 and st["shadow_max_ulp"] == 0, (tag, st)
+        gd, od = g.diagnostics(), o.diagnostics()
+        for k in ("shadow_index_oob", "shadow_x_wrap", "texel_oob", "nan_depth"):
+            assert gd[k] == od[k], (tag, k, gd, od)
+
+    for i in range(5):
+        frame(0.8, 2.1, ("still", i))
+    for i in range(3):
+        frame(0.8 + 0.3 * (i + 1), 2.1, ("camera moves, light fixed", i))
+    frame(1.7, 2.1, "no clear, same light", clear=False)
+    frame(1.7, 0.7, "no clear, light moved", clear=False)          # the buffer now holds the maximum of two passes
+    frame(1.7, 0.7, "no clear, same light again", clear=False)
+    frame(1.7, 0.7, "cleared, same light")
+    frame(1.7, 0.7, "cleared, same light, again")
+    g.clear(); o.clear()
+    assert np.array_equal(g.get_shadow_buffer(), o.get_shadow_buffer())     # materialises the pending clear
+    frame(1.7, 0.7, "after a getter between clear and render", clear=False)
+    frame(1.7, 2.1, "light back")
+    frame(1.7, 2.1, "light back, again")
+    g.close()

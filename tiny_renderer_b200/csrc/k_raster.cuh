@@ -93,6 +93,7 @@ struct RasterArgs {
     // Lone frames: the diagnostics block of the set-up kernel run whose output this launch reads (possibly a run of an
     // earlier frame of the same view, k_setup.cuh SetupOut::diag_zero); folded into diag once per launch.  Null: none.
     const unsigned long long* setup_diag;
+    const unsigned long long* light_diag;  // the same for the light pass (set-up + depth raster) whose shadow buffer this launch reads
     uint32_t* tile_cost;
     const uint32_t* tile_perm; // launch position -> position in the static centre-out order (the index tile_cost is kept under); null: the same
 };
@@ -564,9 +565,15 @@ __global__ void TR_RASTER_BOUNDS k_raster(const RasterArgs a, const ShadeArgs sa
     TR_TIMELINE_MARK(blockIdx.x, 3, timeline_now());
     TR_TIMELINE_MARK(blockIdx.x, 4, (unsigned long long)sm);
 #endif
-    if (LONE && a.setup_diag != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {       // (behind raster_tile's wait for the set-up kernel)
-        const unsigned long long w_zero = a.setup_diag[D_W_ZERO];       // the only counter the set-up kernel feeds
-        if (w_zero) atomicAdd(&a.diag[D_W_ZERO], w_zero);
+    if (LONE && blockIdx.x == 0 && threadIdx.x == 0) {       // (behind raster_tile's wait for the kernels in front)
+        for (int which = 0; which < 2; ++which) {
+            const unsigned long long* from = which ? a.light_diag : a.setup_diag;
+            if (from == nullptr) continue;
+            for (int k = 0; k < D_COUNT; ++k) {
+                const unsigned long long v = from[k];
+                if (v) atomicAdd(&a.diag[k], v);
+            }
+        }
     }
     if (LONE && a.tile_cost != nullptr && threadIdx.x == 0) {
         asm volatile("cp.async.wait_all;" ::: "memory");

@@ -69,6 +69,12 @@ struct tr_scene {
         unsigned long long* setup_diag = nullptr;      // 2 x D_COUNT
         uint32_t setup_runs = 0;
         bool setup_reused = false;                     // the frame being queued re-uses the output (no set-up launch)
+        // Re-use of a lone frame's light pass (render_impl): the shadow buffer holds "cleared + the light pass of
+        // shadow_key" (light, target, up) and nothing has written to it since; its diagnostics blocks and run count
+        SetupKey shadow_key;
+        unsigned long long* light_diag = nullptr;      // 2 x D_COUNT
+        uint32_t light_runs = 0;
+        unsigned long long* light_diag_cur = nullptr;  // non-null while render_impl queues a light pass that counts into its own block
         Bins bins{};
         cudaStream_t stream = nullptr;
         cudaEvent_t done = nullptr;
@@ -233,6 +239,7 @@ int fill_state(tr_scene* s, float z_init, bool do_keys, bool do_shadow, bool do_
     const size_t tile_bytes = (size_t)s->tiles_x * s->tiles_y * 4;
     if (do_keys) CU(cudaMemsetAsync(S(s).tile_state, 0, tile_bytes, s->stream));
     if (do_rgb) CU(cudaMemsetAsync(S(s).rgb_zero, 1, tile_bytes, s->stream));
+    if (do_shadow) S(s).shadow_key.valid = false;       // (the shadow buffer no longer holds a light pass)
     if (do_shadow) CU(cudaMemsetAsync(S(s).shadow_clear, z_init == -3.402823466e38f ? 1 : 0, tile_bytes, s->stream));
     return launch_ok("k_fill_state");
 }
@@ -402,6 +409,8 @@ int create_impl(tr_scene* s, const tr_scene_desc* d) {
         CU(cudaMemset(sl.shadow_clear, 0, n_tiles * 4));
         CU(cudaMalloc(&sl.setup_diag, 2 * D_COUNT * 8));
         CU(cudaMemset(sl.setup_diag, 0, 2 * D_COUNT * 8));
+        CU(cudaMalloc(&sl.light_diag, 2 * D_COUNT * 8));
+        CU(cudaMemset(sl.light_diag, 0, 2 * D_COUNT * 8));
         if ((rc = make_rgb_map(s, &sl))) return rc;
         CU(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
@@ -462,7 +471,7 @@ void destroy_impl(tr_scene* s) {
     for (auto& sl : s->slots) {
         if (sl.stream) { cudaStreamSynchronize(sl.stream); cudaStreamDestroy(sl.stream); }
         if (sl.done) cudaEventDestroy(sl.done);
-        cudaFree(sl.keys); cudaFree(sl.tile_state); cudaFree(sl.rgb); cudaFree(sl.shadow); cudaFree(sl.rgb_zero); cudaFree(sl.shadow_clear); cudaFree(sl.setup_diag);
+        cudaFree(sl.keys); cudaFree(sl.tile_state); cudaFree(sl.rgb); cudaFree(sl.shadow); cudaFree(sl.rgb_zero); cudaFree(sl.shadow_clear); cudaFree(sl.setup_diag); cudaFree(sl.light_diag);
         cudaFree(sl.cam.rec); cudaFree(sl.cam.var); cudaFree(sl.cam.bbox); cudaFree(sl.lit.rec); cudaFree(sl.lit.bbox);
         cudaFree(sl.bins.count); cudaFree(sl.bins.list);
     }
@@ -528,10 +537,11 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     // The set-up output — records, varyings, bounding boxes, bins — is a pure function of model, pipeline, camera and light.
     // A lone frame of a single-pass pipeline whose inputs equal, bit for bit, those of the set-up launch that last wrote
     // this slot re-uses that output: no launch (the app loop with no key down re-renders one view; SURVEY.md 8(d) config 2
-    // times 100 frames of one view).  Two-pass pipelines share the bin lists between their passes and always run both.
+    // times 100 frames of one view).  The two passes of shadow / occlusion share the slot's bin lists: a light pass that
+    // runs invalidates the camera pass's output (below); a light pass that is itself re-used (render_impl) leaves it alone.
     tr_scene::Slot::SetupKey key;
     key.from = s->from; key.at = s->at; key.up = s->up; key.light = s->light; key.pipeline = s->pipeline; key.valid = true;
-    const bool cacheable = g_setup_cache && lone_shape(s) && !light_pass && !kPipelines[s->pipeline].light_pass;
+    const bool cacheable = g_setup_cache && lone_shape(s) && !light_pass;
     if (cacheable && !build_order && setup_key_same(S(s).setup_key, key)) {
         S(s).setup_reused = true;
         s->order_sorted[pass] = reuse_order;
@@ -546,6 +556,10 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     SetupOut out = light_pass ? S(s).lit : S(s).cam;
     unsigned long long* diag = s->diag;
     S(s).setup_key.valid = false;
+    if (light_pass && S(s).light_diag_cur != nullptr) {
+        diag = S(s).light_diag_cur;
+        out.diag_zero = S(s).light_diag + (size_t)((S(s).light_runs + 1u) & 1u) * D_COUNT;
+    }
     if (cacheable) {
         S(s).setup_runs++;
         diag = S(s).setup_diag + (size_t)(S(s).setup_runs & 1u) * D_COUNT;
@@ -658,6 +672,7 @@ int run_views_multi(tr_scene* s, const uint32_t* slots, const Uniforms* lit, con
             S(s).cam.bins = S(s).bins;
             S(s).lit.bins = S(s).bins;
             S(s).setup_key.valid = false;       // (the slot's set-up output is overwritten)
+            if (light) S(s).shadow_key.valid = false;
             sb.v[j].out = light ? S(s).lit : S(s).cam;
             sb.v[j].u = u;
             vb.v[j].a = raster_args(s, light, 0, true, true);
@@ -695,6 +710,12 @@ int run_raster(tr_scene* s, int mode, uint32_t epoch, bool fresh, const Uniforms
     const int pass = depth_only ? 0 : 1;
     if (S(s).setup_key.valid && !depth_only)      // (valid: the slot's set-up output comes from a lone camera pass that counted into its own block)
         a.setup_diag = S(s).setup_diag + (size_t)(S(s).setup_runs & 1u) * D_COUNT;
+    if (depth_only) {
+        S(s).shadow_key.valid = false;              // (render_impl sets it again when this is a light pass it may re-use)
+        if (S(s).light_diag_cur != nullptr) a.diag = S(s).light_diag_cur;
+    } else if (S(s).shadow_key.valid && kPipelines[s->pipeline].light_pass && mode >= 0) {
+        a.light_diag = S(s).light_diag + (size_t)(S(s).light_runs & 1u) * D_COUNT;
+    }
     if (lone_costs(s)) {
         if (s->order_sorted[pass]) {
             a.tile_order = s->tile_order_sorted + (size_t)pass * a.n_tiles;
@@ -772,8 +793,23 @@ int render_impl(tr_scene* s) {
     if (pipe.light_pass) {
         if ((rc = prep_error(prepare_light(u, s->width, s->height, s->light, s->at, s->up)))) return rc;
         u.n_triangles = s->n_tri; u.epoch = s->epoch;
-        if ((rc = run_setup(s, u, true))) return rc;
-        if ((rc = run_raster(s, kModeDepthOnly, s->epoch, s->fresh_shadow, u, false))) return rc;
+        // The shadow buffer of a lone frame is a pure function of model, light, target and up when the pass starts from a
+        // cleared buffer — and merging the same pass into it again (a render without clear) changes nothing.  While those
+        // inputs stay bit-identical and nothing else has written to the buffer, later frames re-use it: no set-up launch,
+        // no depth raster (a camera that moves under a fixed light; the app loop with no key down).
+        tr_scene::Slot& sl = S(s);
+        tr_scene::Slot::SetupKey lk;
+        lk.light = s->light; lk.at = s->at; lk.up = s->up; lk.pipeline = -2; lk.valid = true;
+        const bool may_cache = g_setup_cache && lone_shape(s) && s->n_tri != 0;
+        if (!(may_cache && setup_key_same(sl.shadow_key, lk))) {
+            const bool keep = may_cache && s->fresh_shadow;     // "cleared + this pass" is what the buffer will hold
+            if (keep) { sl.light_runs++; sl.light_diag_cur = sl.light_diag + (size_t)(sl.light_runs & 1u) * D_COUNT; }
+            rc = run_setup(s, u, true);
+            if (rc == TR_OK) rc = run_raster(s, kModeDepthOnly, s->epoch, s->fresh_shadow, u, false);
+            sl.light_diag_cur = nullptr;
+            if (rc) return rc;
+            if (keep) sl.shadow_key = lk;
+        }
         s->fresh_shadow = false;
     }
     if ((rc = prep_error(pipe.prepare(u, s->width, s->height, s->light, s->from, s->at, s->up)))) return rc;
