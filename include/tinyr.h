@@ -75,6 +75,9 @@ int tr_scene_clear(tr_scene* s);                                                
 int tr_scene_set_light_direction(tr_scene* s, const float dir[3]);               /* set_light_direction   scene.rs:140 */
 int tr_scene_set_camera(tr_scene* s, const float look_from[3], const float look_at[3], const float up[3]); /* scene.rs:145 */
 int tr_scene_render(tr_scene* s);                                                /* Scene::render         scene.rs:151 */
+/* (tr_scene_render computes what Scene::render computes; passes whose inputs are bit-identical to the previous frame's —
+ * the vertex stage of an unchanged view, the light pass of an unchanged light — are not run again, their output is
+ * re-used; buffers, getters and diagnostics are the same as if they had run.  TINYR_SETUP_CACHE=0 disables that.) */
 int tr_scene_get_frame_buffer(tr_scene* s, uint8_t* dst_rgb8_topdown);           /* get_frame_buffer      scene.rs:92  */
 int tr_scene_get_z_buffer(tr_scene* s, uint8_t* dst_rgb8_topdown);               /* get_z_buffer          scene.rs:101 */
 int tr_scene_get_shadow_buffer(tr_scene* s, uint8_t* dst_rgb8_topdown);          /* get_shadow_buffer     scene.rs:115 */
