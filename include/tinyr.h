@@ -193,7 +193,9 @@ int tr_scene_set_stream(tr_scene* s, void* cuda_stream);                        
 int tr_scene_device_frame(tr_scene* s, void** device_ptr_rgb8_topdown);
 /* Test hooks: bit 0 makes the occlusion samples always take the range-tested division (k_shade.cuh occlusion_gray picks
  * between two forms of the same arithmetic per pixel; results must not depend on the choice); bit 1 makes single-frame
- * renders launch the tile kernel in its batch CTA shape (128 threads), so that shape can be timed on a lone frame. */
+ * renders launch the tile kernel in its batch CTA shape (128 threads), so that shape can be timed on a lone frame; bit 2
+ * makes every lone frame run all its passes in the static launch order (no re-use of unchanged passes, no cost-sorted
+ * order), so both forms can be timed and compared in one process. */
 int tr_scene_set_debug_flags(tr_scene* s, uint32_t flags);           /* zero-copy access for tests / interop */
 int tr_scene_timer_begin(tr_scene* s);                                            /* CUDA event on the scene stream */
 int tr_scene_timer_end(tr_scene* s, float* elapsed_ms);                           /* records + synchronises */

@@ -572,3 +572,24 @@ def test_light_pass_is_reused_only_while_the_shadow_buffer_stands(tinyr, oracle,
     frame(1.7, 2.1, "light back")
     frame(1.7, 2.1, "light back, again")
     g.close()
+
+
+@pytest.mark.parametrize("pipeline", ["darboux", "shadow"])
+def test_debug_bit_2_runs_every_pass_and_changes_nothing(tinyr, pipeline):
+    """Debug bit 2 disables the cost-sorted launch order and the re-use of unchanged passes for a scene; frames, depth and
+    diagnostics must not depend on it."""
+    from tiny_renderer_b200.scene import Scene
+    model = get_model("diablo")
+    w, h = 2560, 1440
+    a, b = Scene(w, h, model, pipeline), Scene(w, h, model, pipeline)
+    b.set_debug_flags(4)
+    for cam, light in [(0.8, 2.1)] * 5 + [(1.1, 2.1), (1.1, 0.7), (1.1, 0.7)]:
+        lf, la, up, l = assets.view_vectors(cam, light)
+        parity.drive(a, lf, la, up, l)
+        parity.drive(b, lf, la, up, l)
+        assert np.array_equal(a.raw_frame(), b.raw_frame()) and np.array_equal(a.raw_z(), b.raw_z())
+        assert np.array_equal(a.raw_visibility(), b.raw_visibility())
+        if pipeline == "shadow":
+            assert np.array_equal(a.raw_shadow(), b.raw_shadow())
+        assert a.diagnostics() == b.diagnostics()
+    a.close(); b.close()

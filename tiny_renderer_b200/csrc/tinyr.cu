@@ -496,7 +496,7 @@ bool setup_key_same(const tr_scene::Slot::SetupKey& a, const tr_scene::Slot::Set
 // lone frames of at least two waves of tiles (800x800: 325 tiles, one wave whatever the order) record tile costs
 bool lone_costs(const tr_scene* s) {
     const uint32_t n_tiles = s->tiles_x * s->tiles_y;
-    return lone_shape(s) && g_lone_sort && n_tiles > 1024u && n_tiles <= (uint32_t)kSortMaxTiles;
+    return lone_shape(s) && g_lone_sort && (s->debug_flags & 4u) == 0u && n_tiles > 1024u && n_tiles <= (uint32_t)kSortMaxTiles;
 }
 tr_scene::CostView pass_view(const tr_scene* s, int pass) {
     tr_scene::CostView v;
@@ -541,7 +541,7 @@ int run_setup(tr_scene* s, const Uniforms& u, bool light_pass) {
     // runs invalidates the camera pass's output (below); a light pass that is itself re-used (render_impl) leaves it alone.
     tr_scene::Slot::SetupKey key;
     key.from = s->from; key.at = s->at; key.up = s->up; key.light = s->light; key.pipeline = s->pipeline; key.valid = true;
-    const bool cacheable = g_setup_cache && lone_shape(s) && !light_pass;
+    const bool cacheable = g_setup_cache && (s->debug_flags & 4u) == 0u && lone_shape(s) && !light_pass;
     if (cacheable && !build_order && setup_key_same(S(s).setup_key, key)) {
         S(s).setup_reused = true;
         s->order_sorted[pass] = reuse_order;
@@ -800,7 +800,7 @@ int render_impl(tr_scene* s) {
         tr_scene::Slot& sl = S(s);
         tr_scene::Slot::SetupKey lk;
         lk.light = s->light; lk.at = s->at; lk.up = s->up; lk.pipeline = -2; lk.valid = true;
-        const bool may_cache = g_setup_cache && lone_shape(s) && s->n_tri != 0;
+        const bool may_cache = g_setup_cache && (s->debug_flags & 4u) == 0u && lone_shape(s) && s->n_tri != 0;
         if (!(may_cache && setup_key_same(sl.shadow_key, lk))) {
             const bool keep = may_cache && s->fresh_shadow;     // "cleared + this pass" is what the buffer will hold
             if (keep) { sl.light_runs++; sl.light_diag_cur = sl.light_diag + (size_t)(sl.light_runs & 1u) * D_COUNT; }
