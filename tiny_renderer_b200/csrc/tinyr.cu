@@ -490,7 +490,7 @@ bool lone_shape(const tr_scene* s) { return !s->overlapping && (s->debug_flags &
 // TINYR_SETUP_CACHE=0: every lone frame runs the set-up kernel (A/B in profiles/r2_probes.md).
 static const bool g_setup_cache = !(getenv("TINYR_SETUP_CACHE") && atoi(getenv("TINYR_SETUP_CACHE")) == 0);
 bool setup_key_same(const tr_scene::Slot::SetupKey& a, const tr_scene::Slot::SetupKey& b) {
-    auto eq = [](f3 p, f3 q) { return p.x == q.x && p.y == q.y && p.z == q.z; };
+    auto eq = [](f3 p, f3 q) { return memcmp(&p, &q, sizeof(f3)) == 0; };      // bit for bit: -0.0 is not 0.0 here
     return a.valid && b.valid && a.pipeline == b.pipeline && eq(a.from, b.from) && eq(a.at, b.at) && eq(a.up, b.up) && eq(a.light, b.light);
 }
 // lone frames of at least two waves of tiles (800x800: 325 tiles, one wave whatever the order) record tile costs
@@ -505,7 +505,7 @@ tr_scene::CostView pass_view(const tr_scene* s, int pass) {
     return v;
 }
 bool view_same(const tr_scene::CostView& a, const tr_scene::CostView& b) {
-    auto eq = [](f3 p, f3 q) { return p.x == q.x && p.y == q.y && p.z == q.z; };
+    auto eq = [](f3 p, f3 q) { return memcmp(&p, &q, sizeof(f3)) == 0; };
     return a.valid && b.valid && a.pipeline == b.pipeline && eq(a.eye, b.eye) && eq(a.at, b.at) && eq(a.up, b.up);
 }
 // The previous frame's costs predict this frame's when the view moved little: measured on the 4K turntable, 1 degree per
