@@ -670,6 +670,15 @@ def run_shadow4k(rank, world, dev, model, dist, tstream, steps):
         out["roofline"] = {"bound": "hbm", "algorithmic_bytes_per_frame": nbytes, "achieved": nbytes / (out["us_per_frame"] * 1e-6) / 1e9,
                            "peak": peak, "unit": "GB/s", "frac": nbytes / (out["us_per_frame"] * 1e-6) / 1e9 / peak,
                            "note": "overlapped batch (k_raster<-2,128> + k_raster<5,128>); bytes = 27 P + min(3 C, 3 MiB) + geometry of both passes"}
+        b2b = back_to_back_us(s, views[8])
+        s.set_debug_flags(4)
+        b2b_all = back_to_back_us(s, views[8])
+        s.set_debug_flags(0)
+        out["single_view"] = {"us_per_frame": b2b, "us_per_frame_every_pass_run": b2b_all, "frames": 100, "reps": 5,
+                              "frac": nbytes / (b2b * 1e-6) / 1e9 / peak, "frac_every_pass_run": nbytes / (b2b_all * 1e-6) / 1e9 / peak,
+                              "note": "100 back-to-back lone frames of one view under one light, events around all of them, median of 5: frames 2.. "
+                                      "re-use the shadow buffer (no light set-up, no depth raster), the camera pass's set-up output and a "
+                                      "cost-sorted tile order; `*_every_pass_run` (debug bit 2): K1 + K4 + K1 + K3/K5 every frame, static order"}
         out["shadow_index_oob"] = diag["shadow_index_oob"]
     s.close()
     return out
