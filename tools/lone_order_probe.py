@@ -28,7 +28,7 @@ def run(tag, env):
 for PIPE in sys.argv[1:] or ["phong", "darboux"]:
     t = run("centre-out", {"TINYR_LONE_SORT": "0"})
     dur = (t[:, 3] - np.maximum(t[:, 1], t[:, 0])) / 1e3
-    for tag, key in (("longest first", -dur), ("4 us buckets", -np.floor(dur / 4.0))):
+    for tag, key in (("longest first", -dur), ("4 us buckets", -np.floor(dur / 4.0)), ("tiles with geometry first, centre-out inside", -(t[:, 5] > 0).astype(np.int64))):
         perm = np.argsort(key, kind="stable").astype(np.uint32)
         f = os.path.join(OUT, "perm.bin")
         perm.tofile(f)
